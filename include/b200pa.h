@@ -1,0 +1,194 @@
+/*
+ * b200pa.h — C-ABI of the B200-native (sm_100a) paged-attention hot path.
+ *
+ * This is the drop-in boundary underneath the reference's `vllm._C` operator
+ * module (DeepAuto-AI/vllm-legacy, vLLM 0.4.3 fork).  Plain pointers and sizes,
+ * no torch types.  Every entry point names the reference interface it replaces.
+ * All device entry points are asynchronous on `stream`, allocate nothing, do no
+ * host synchronisation and are CUDA-graph capturable (except swap_blocks, which
+ * is a host loop of async copies exactly like the reference's).
+ *
+ * Return value: B200PA_OK (0) or a negative b200pa_status_t.  The PyTorch
+ * binding (vllm_legacy_b200/csrc/torch_binding.cpp) maps the codes to the
+ * reference's TORCH_CHECK texts (attention_kernels.cu:764,801;
+ * quant_utils.cuh:538,564; cache_kernels.cu:31-45).
+ */
+#ifndef B200PA_H_
+#define B200PA_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200PA_ABI_VERSION 1
+
+/* CUDA stream handle (== cudaStream_t == CUstream). */
+typedef struct CUstream_st* b200pa_stream_t;
+
+/* scalar_t of query/out/key/value (reference: VLLM_DISPATCH_FLOATING_TYPES,
+ * csrc/dispatch_utils.h) and raw-byte cache element (uint8). */
+typedef enum {
+  B200PA_F16 = 0,
+  B200PA_BF16 = 1,
+  B200PA_F32 = 2,
+  B200PA_U8 = 3
+} b200pa_dtype_t;
+
+/* kv_cache_dtype string of the reference ("auto" | "fp8"/"fp8_e4m3" | "fp8_e5m2"),
+ * csrc/attention/dtype_fp8.cuh:14-18, quant_utils.cuh:529-566. */
+typedef enum {
+  B200PA_KV_AUTO = 0,
+  B200PA_KV_FP8_E4M3 = 1,
+  B200PA_KV_FP8_E5M2 = 2
+} b200pa_kv_dtype_t;
+
+typedef enum {
+  B200PA_OK = 0,
+  B200PA_ERR_HEAD_SIZE = -1,   /* "Unsupported head size: "            attention_kernels.cu:764 */
+  B200PA_ERR_BLOCK_SIZE = -2,  /* "Unsupported block size: "           attention_kernels.cu:801 */
+  B200PA_ERR_KV_DTYPE = -3,    /* "Unsupported data type of kv cache: " quant_utils.cuh:564     */
+  B200PA_ERR_INPUT_DTYPE = -4, /* "Unsupported input type of kv cache: " quant_utils.cuh:538    */
+  B200PA_ERR_INVALID_ARG = -5, /* null pointer / negative size / misaligned cache               */
+  B200PA_ERR_CUDA = -6,        /* a CUDA runtime call failed: see b200pa_last_cuda_error()      */
+  B200PA_ERR_DEVICE_COMBINATION = -7 /* "Invalid device combination"   cache_kernels.cu:41-43   */
+} b200pa_status_t;
+
+/*
+ * paged_attention_v1 / paged_attention_v2
+ * replaces: csrc/ops.h:5-30, csrc/attention/attention_kernels.cu:805-825 (v1),
+ *           :984-1014 (v2, the fork's pointer-string ABI) and the kernels at
+ *           :86-496, :565-669.
+ *
+ * Layouts (x = 16 / sizeof(cache element)):
+ *   out, query      [num_seqs, num_heads, head_size]     dtype; query row stride q_stride
+ *   key_cache       [num_blocks, num_kv_heads, head_size/x, block_size, x]
+ *   value_cache     [num_blocks, num_kv_heads, head_size, block_size]
+ *                   both with strides kv_block_stride / kv_head_stride (elements),
+ *                   innermost three/two dims contiguous (as the reference assumes)
+ *   block_tables    [num_seqs, max_num_blocks_per_seq] int32
+ *   seq_lens        [num_seqs] int32
+ *   alibi_slopes    [num_heads] float or NULL
+ *   v2 scratch      exp_sums, max_logits [num_seqs, num_heads, max_num_partitions] float
+ *                   tmp_out [num_seqs, num_heads, max_num_partitions, head_size] dtype
+ *                   with max_num_partitions = ceil(max_seq_len / 512) as the
+ *                   reference's callers size it (vllm/attention/ops/paged_attn.py:111-158).
+ */
+typedef struct {
+  void* out;
+  const void* query;
+  const void* key_cache;
+  const void* value_cache;
+  const int32_t* block_tables;
+  const int32_t* seq_lens;
+  const float* alibi_slopes; /* nullable */
+  float* exp_sums;           /* v2 only */
+  float* max_logits;         /* v2 only */
+  void* tmp_out;             /* v2 only */
+  int64_t q_stride;          /* elements between query rows (query.stride(0)) */
+  int64_t kv_block_stride;   /* key_cache.stride(0), elements */
+  int64_t kv_head_stride;    /* key_cache.stride(1), elements */
+  int32_t num_seqs;
+  int32_t num_heads;
+  int32_t num_kv_heads;
+  int32_t head_size;
+  int32_t block_size;
+  int32_t max_seq_len;
+  int32_t max_num_blocks_per_seq;
+  int32_t max_num_partitions; /* v2 only: partition dim of the scratch buffers */
+  int32_t dtype;              /* b200pa_dtype_t of query/out */
+  int32_t kv_dtype;           /* b200pa_kv_dtype_t */
+  float scale;
+  float kv_scale;
+  int32_t tp_rank;
+  int32_t blocksparse_local_blocks;
+  int32_t blocksparse_vert_stride; /* > 1 enables block-sparse */
+  int32_t blocksparse_block_size;
+  int32_t blocksparse_head_sliding_step;
+} b200pa_attn_params_t;
+
+int b200pa_paged_attention_v1(const b200pa_attn_params_t* p, b200pa_stream_t stream);
+int b200pa_paged_attention_v2(const b200pa_attn_params_t* p, b200pa_stream_t stream);
+
+/*
+ * reshape_and_cache
+ * replaces: csrc/cache.h:15-25, csrc/cache_kernels.cu:150-202, 241-287.
+ *   key, value   [num_tokens, num_heads, head_size] dtype, row strides key_stride/value_stride
+ *   key_cache    [num_blocks, num_heads, head_size/x, block_size, x]   (contiguous)
+ *   value_cache  [num_blocks, num_heads, head_size, block_size]        (contiguous)
+ *   slot_mapping [num_tokens] int64, slot < 0 = padding token (skipped)
+ * kv_dtype AUTO stores dtype elements; FP8_* stores uint8 = cvt(float(v) / kv_scale).
+ */
+typedef struct {
+  const void* key;
+  const void* value;
+  void* key_cache;
+  void* value_cache;
+  const int64_t* slot_mapping;
+  int64_t key_stride;
+  int64_t value_stride;
+  int32_t num_tokens;
+  int32_t num_heads;
+  int32_t head_size;
+  int32_t block_size;
+  int32_t x;
+  int32_t dtype;    /* b200pa_dtype_t of key/value */
+  int32_t kv_dtype; /* b200pa_kv_dtype_t */
+  float kv_scale;
+} b200pa_reshape_params_t;
+
+int b200pa_reshape_and_cache(const b200pa_reshape_params_t* p, b200pa_stream_t stream);
+
+/*
+ * copy_blocks
+ * replaces: csrc/cache.h:11-13, csrc/cache_kernels.cu:68-146.
+ *   key_cache_ptrs / value_cache_ptrs : HOST arrays of num_layers device pointers
+ *   block_mapping                     : DEVICE int64 [num_pairs, 2] (src, dst)
+ *   block_bytes                       : bytes of one block of one layer's K (== V) cache
+ * The pointer arrays travel as kernel parameters: no H2D copy, no sync.
+ */
+int b200pa_copy_blocks(void* const* key_cache_ptrs, void* const* value_cache_ptrs,
+                       int32_t num_layers, const int64_t* block_mapping,
+                       int64_t num_pairs, int64_t block_bytes, b200pa_stream_t stream);
+
+/*
+ * swap_blocks
+ * replaces: csrc/cache.h:8-9, csrc/cache_kernels.cu:25-64.
+ *   block_mapping : HOST int64 [num_pairs, 2]
+ *   kind          : 0 device->device, 1 device->host, 2 host->device
+ * Consecutive (src+1, dst+1) runs are merged into one cudaMemcpyAsync.
+ */
+typedef enum { B200PA_D2D = 0, B200PA_D2H = 1, B200PA_H2D = 2 } b200pa_copy_kind_t;
+
+int b200pa_swap_blocks(const void* src, void* dst, const int64_t* block_mapping_host,
+                       int64_t num_pairs, int64_t block_bytes, int32_t kind,
+                       b200pa_stream_t stream);
+
+/*
+ * convert_fp8 ("only for testing" in the reference)
+ * replaces: csrc/cache.h:41-42, csrc/cache_kernels.cu:347-420.
+ * Exactly one of src_dtype / dst_dtype is B200PA_U8; the other is F16/BF16/F32.
+ *   to fp8  : dst = cvt_satfinite(float(src) / scale)
+ *   from fp8: dst = T(float(half(src)) * scale)
+ */
+int b200pa_convert_fp8(void* dst, const void* src, int64_t numel, int32_t dst_dtype,
+                       int32_t src_dtype, float scale, int32_t kv_dtype,
+                       b200pa_stream_t stream);
+
+/* replaces: csrc/cuda_utils.h, csrc/cuda_utils_kernels.cu:17-29 */
+int b200pa_get_max_shared_memory_per_block_device_attribute(int32_t device_id);
+
+/* Diagnostics */
+int b200pa_abi_version(void);
+const char* b200pa_status_string(int status);
+int b200pa_last_cuda_error(void); /* cudaError_t of the last B200PA_ERR_CUDA on this thread */
+/* Name of the kernel family the last attention call on this thread dispatched
+ * to ("mma_tma" | "simt"), and the split it used; for tests and the bench. */
+const char* b200pa_last_attention_path(void);
+int b200pa_last_attention_partitions(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PA_H_ */

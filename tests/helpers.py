@@ -1,0 +1,161 @@
+"""Shared test fixtures: restatements of the reference's test helpers for this path.
+
+  create_kv_caches_with_random  <- vllm/utils.py:398-446 (+ _generate_random_fp8, :324-341)
+  ref_single_query_cached_kv_attention / ref_masked_attention
+                                <- tests/kernels/test_attention.py:43-111
+  load_ref_cpu / load_ref_cuda  -> the reference's own sources compiled into oracle/_ref/
+"""
+import importlib.util
+import os
+import random
+import sys
+from typing import List, Optional, Tuple
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+REF_DIR = os.path.join(ROOT, "oracle", "_ref")
+
+
+def _load_so(name: str, path: str):
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def cpu_flags() -> set:
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("flags"):
+                    return set(line.split(":", 1)[1].split())
+    except OSError:
+        pass
+    return set()
+
+
+def load_ref_cpu():
+    """The reference's csrc/cpu/attention.cpp + cache.cpp (unchanged) — or None if not built /
+    the host lacks AVX512."""
+    flags = cpu_flags()
+    if not {"avx512f", "avx512bw", "avx512vl", "avx512dq"} <= flags:
+        return None
+    name = "ref_cpu_bf16" if "avx512_bf16" in flags else "ref_cpu"
+    path = os.path.join(REF_DIR, name + ".so")
+    if not os.path.exists(path):
+        return None
+    return _load_so(name, path)
+
+
+def load_ref_cuda():
+    """The reference's csrc/attention/attention_kernels.cu + cache_kernels.cu built for sm_100a."""
+    path = os.path.join(REF_DIR, "ref_cuda.so")
+    if not os.path.exists(path) or not torch.cuda.is_available():
+        return None
+    return _load_so("ref_cuda", path)
+
+
+STR_DTYPE_TO_TORCH_DTYPE = {"half": torch.half, "bfloat16": torch.bfloat16, "float": torch.float}
+
+
+def create_kv_caches_with_random(num_blocks: int, block_size: int, num_layers: int, num_heads: int,
+                                 head_size: int, cache_dtype: str, model_dtype, seed: int = 0,
+                                 device: str = "cuda", convert_fp8=None
+                                 ) -> Tuple[List[torch.Tensor], List[torch.Tensor]]:
+    """vllm/utils.py:398-446: K [nb, H, D/x, B, x], V [nb, H, D, B], uniform(-D^-0.5, D^-0.5);
+    fp8 caches are generated in fp16 and converted with convert_fp8 (vllm/utils.py:324-341)."""
+    torch.random.manual_seed(seed)
+    if torch.cuda.is_available():
+        torch.cuda.manual_seed(seed)
+    if isinstance(model_dtype, str):
+        model_dtype = STR_DTYPE_TO_TORCH_DTYPE[model_dtype]
+    if cache_dtype == "auto":
+        torch_dtype = model_dtype
+    elif cache_dtype in ("half", "bfloat16", "float"):
+        torch_dtype = STR_DTYPE_TO_TORCH_DTYPE[cache_dtype]
+    elif cache_dtype == "fp8":
+        torch_dtype = torch.uint8
+    else:
+        raise ValueError(f"Invalid kv cache dtype: {cache_dtype}")
+    scale = head_size ** -0.5
+    x = 16 // torch.tensor([], dtype=torch_dtype).element_size()
+    key_cache_shape = (num_blocks, num_heads, head_size // x, block_size, x)
+    value_cache_shape = (num_blocks, num_heads, head_size, block_size)
+
+    def _fill(shape):
+        t = torch.empty(size=shape, dtype=torch_dtype, device=device)
+        if cache_dtype == "fp8":
+            tmp = torch.empty_like(t, dtype=torch.float16)
+            tmp.uniform_(-scale, scale)
+            assert convert_fp8 is not None, "fp8 caches need a convert_fp8 op"
+            convert_fp8(t, tmp)
+        else:
+            t.uniform_(-scale, scale)
+        return t
+
+    key_caches = [_fill(key_cache_shape) for _ in range(num_layers)]
+    value_caches = [_fill(value_cache_shape) for _ in range(num_layers)]
+    return key_caches, value_caches
+
+
+def ref_masked_attention(query, key, value, scale, attn_mask=None):
+    """tests/kernels/test_attention.py:43-55"""
+    attn_weights = scale * torch.einsum("qhd,khd->hqk", query, key).float()
+    if attn_mask is not None:
+        attn_weights = attn_weights + attn_mask.float()
+    attn_weights = torch.softmax(attn_weights, dim=-1).to(value.dtype)
+    return torch.einsum("hqk,khd->qhd", attn_weights, value)
+
+
+def ref_single_query_cached_kv_attention(output, query, num_queries_per_kv, key_cache, value_cache,
+                                         block_tables, seq_lens, scale, alibi_slopes) -> None:
+    """tests/kernels/test_attention.py:58-111 (gathers token by token; small cases only)."""
+    num_query_heads = query.shape[1]
+    num_kv_heads = value_cache.shape[1]
+    head_size = value_cache.shape[2]
+    block_size = value_cache.shape[3]
+    num_seqs = query.shape[0]
+    block_tables_lst = block_tables.cpu().tolist()
+    seq_lens_lst = seq_lens.cpu().tolist()
+    for i in range(num_seqs):
+        q = query[i].unsqueeze(0)
+        block_table = block_tables_lst[i]
+        seq_len = int(seq_lens_lst[i])
+        if seq_len == 0:
+            output[i].zero_()
+            continue
+        idx = torch.arange(seq_len, device=query.device)
+        blocks = torch.tensor(block_table, device=query.device, dtype=torch.long)[idx // block_size]
+        offs = idx % block_size
+        # key_cache[b, :, :, off, :] -> [H, D/x, x] -> [H, D]
+        keys = key_cache[blocks, :, :, offs, :].reshape(seq_len, num_kv_heads, head_size)
+        values = value_cache[blocks, :, :, offs]
+        if num_queries_per_kv > 1:
+            keys = torch.repeat_interleave(keys, num_queries_per_kv, dim=1)
+            values = torch.repeat_interleave(values, num_queries_per_kv, dim=1)
+        alibi_bias = None
+        if alibi_slopes is not None:
+            position_ids = torch.arange(seq_len, device=query.device).int()
+            alibi_bias = (position_ids - seq_len + 1).float()
+            alibi_bias = alibi_slopes.view(-1, 1, 1) * alibi_bias.view(1, 1, -1)
+        out = ref_masked_attention(q, keys, values, scale, alibi_bias)
+        output[i].copy_(out.view(num_query_heads, head_size), non_blocking=True)
+
+
+def make_block_tables(num_seqs: int, max_num_blocks_per_seq: int, num_blocks: int, seed: int = 0,
+                      distinct: bool = False) -> List[List[int]]:
+    """Random block tables (test_attention.py:159-167, with replacement) or, for bandwidth
+    measurements, a permutation of distinct physical blocks."""
+    rng = random.Random(seed)
+    if distinct:
+        assert num_seqs * max_num_blocks_per_seq <= num_blocks
+        perm = list(range(num_blocks))
+        rng.shuffle(perm)
+        return [perm[i * max_num_blocks_per_seq:(i + 1) * max_num_blocks_per_seq]
+                for i in range(num_seqs)]
+    return [[rng.randint(0, num_blocks - 1) for _ in range(max_num_blocks_per_seq)]
+            for _ in range(num_seqs)]

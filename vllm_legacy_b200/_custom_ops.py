@@ -1,0 +1,127 @@
+"""Python wrappers of the hot-path custom ops — same names, argument order, defaults and
+marshalling as the reference's `vllm/_custom_ops.py:37-99, 304-354` (including the fork's
+habit of passing the KV-cache pointers of paged_attention_v2 / reshape_and_cache as decimal strings
+so duck-typed managed-memory caches work: vllm/worker/cache_engine/map_cache_engine.py:35-66).
+
+The ops come from the compiled sm_100a extension; importing this module fails loudly without it.
+"""
+from typing import List, Optional
+
+import torch
+
+from . import load_extension
+
+_C = load_extension()
+vllm_ops = _C.ops
+vllm_cache_ops = _C.cache_ops
+vllm_cuda_utils = _C.cuda_utils
+
+
+# page attention ops
+def paged_attention_v1(
+    out: torch.Tensor,
+    query: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    num_kv_heads: int,
+    scale: float,
+    block_tables: torch.Tensor,
+    seq_lens: torch.Tensor,
+    block_size: int,
+    max_seq_len: int,
+    alibi_slopes: Optional[torch.Tensor],
+    kv_cache_dtype: str,
+    kv_scale: float,
+    tp_rank: int = 0,
+    blocksparse_local_blocks: int = 0,
+    blocksparse_vert_stride: int = 0,
+    blocksparse_block_size: int = 64,
+    blocksparse_head_sliding_step: int = 0,
+) -> None:
+    vllm_ops.paged_attention_v1(
+        out, query, key_cache, value_cache, num_kv_heads, scale, block_tables,
+        seq_lens, block_size, max_seq_len, alibi_slopes, kv_cache_dtype,
+        kv_scale, tp_rank, blocksparse_local_blocks, blocksparse_vert_stride,
+        blocksparse_block_size, blocksparse_head_sliding_step)
+
+
+def paged_attention_v2(
+    out: torch.Tensor,
+    exp_sum: torch.Tensor,
+    max_logits: torch.Tensor,
+    tmp_out: torch.Tensor,
+    query: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    num_kv_heads: int,
+    scale: float,
+    block_tables: torch.Tensor,
+    seq_lens: torch.Tensor,
+    block_size: int,
+    max_seq_len: int,
+    alibi_slopes: Optional[torch.Tensor],
+    kv_cache_dtype: str,
+    kv_scale: float,
+    tp_rank: int = 0,
+    blocksparse_local_blocks: int = 0,
+    blocksparse_vert_stride: int = 0,
+    blocksparse_block_size: int = 64,
+    blocksparse_head_sliding_step: int = 0,
+) -> None:
+    # key_cache / value_cache only need data_ptr() and stride(): tensors or ManagedTensor-likes.
+    vllm_ops.paged_attention_v2(
+        out, exp_sum, max_logits, tmp_out, query,
+        str(key_cache.data_ptr()), key_cache.stride(0), key_cache.stride(1),
+        str(value_cache.data_ptr()),
+        num_kv_heads, scale, block_tables, seq_lens, block_size, max_seq_len,
+        alibi_slopes, kv_cache_dtype, kv_scale, tp_rank,
+        blocksparse_local_blocks, blocksparse_vert_stride,
+        blocksparse_block_size, blocksparse_head_sliding_step)
+
+
+# cache ops
+def reshape_and_cache(
+    key: torch.Tensor,
+    value: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    slot_mapping: torch.Tensor,
+    kv_cache_dtype: str,
+    kv_scale: float,
+) -> None:
+    vllm_cache_ops.reshape_and_cache(
+        key, value,
+        str(key_cache.data_ptr()), key_cache.size(3), key_cache.size(4),
+        str(value_cache.data_ptr()),
+        slot_mapping, kv_cache_dtype, kv_scale)
+
+
+def copy_blocks(key_caches: List[torch.Tensor], value_caches: List[torch.Tensor],
+                block_mapping: torch.Tensor) -> None:
+    vllm_cache_ops.copy_blocks(key_caches, value_caches, block_mapping)
+
+
+def swap_blocks(src: torch.Tensor, dst: torch.Tensor,
+                block_mapping: torch.Tensor) -> None:
+    vllm_cache_ops.swap_blocks(src, dst, block_mapping)
+
+
+def convert_fp8(output: torch.Tensor,
+                input: torch.Tensor,
+                scale: float = 1.0,
+                kv_dtype: str = "fp8") -> None:
+    vllm_cache_ops.convert_fp8(output, input, scale, kv_dtype)
+
+
+# cuda utils (vllm/utils.py:149-160 calls this through vllm._C.cuda_utils)
+def get_max_shared_memory_per_block_device_attribute(device_id: int) -> int:
+    return vllm_cuda_utils.get_max_shared_memory_per_block_device_attribute(device_id)
+
+
+# diagnostics (not in the reference)
+def last_attention_path() -> str:
+    return _C.last_attention_path()
+
+
+def last_attention_partitions() -> int:
+    return _C.last_attention_partitions()

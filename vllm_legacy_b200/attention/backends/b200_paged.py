@@ -1,0 +1,149 @@
+"""`B200PagedAttentionBackend` — a decode backend with the shape of the reference's backends that
+route decode through `PagedAttention` (`vllm/attention/backends/xformers.py:19-58, 196-335`;
+the fork's `hip.py:166-174, 306-319` dense path; `blocksparse_attn.py:357-390`).
+
+It writes the step's K/V into the paged cache (`reshape_and_cache`) and runs decode attention
+(`paged_attention_v1/v2`) on the B200 kernels.  Prefill attention (xformers / flash / HiP Triton) is
+third-party code outside this path: a batch that contains prefill tokens still gets its K/V cached,
+and the prefill rows of the output are left to the caller's prefill implementation.
+"""
+from dataclasses import dataclass
+from typing import Any, Dict, List, Literal, Optional, Tuple, Type
+
+import torch
+
+from vllm_legacy_b200.attention.backends.abstract import (AttentionBackend, AttentionImpl,
+                                                           AttentionMetadata)
+from vllm_legacy_b200.attention.ops.paged_attn import PagedAttention, PagedAttentionMetadata
+
+
+class B200PagedAttentionBackend(AttentionBackend):
+
+    @staticmethod
+    def get_name() -> str:
+        return "b200-paged"
+
+    @staticmethod
+    def get_impl_cls() -> Type["B200PagedAttentionImpl"]:
+        return B200PagedAttentionImpl
+
+    @staticmethod
+    def make_metadata(*args, **kwargs) -> "B200PagedAttentionMetadata":
+        return B200PagedAttentionMetadata(*args, **kwargs)
+
+    @staticmethod
+    def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int,
+                           head_size: int) -> Tuple[int, ...]:
+        return PagedAttention.get_kv_cache_shape(num_blocks, block_size, num_kv_heads, head_size)
+
+    @staticmethod
+    def swap_blocks(src_kv_cache: torch.Tensor, dst_kv_cache: torch.Tensor,
+                    src_to_dst: torch.Tensor) -> None:
+        PagedAttention.swap_blocks(src_kv_cache, dst_kv_cache, src_to_dst)
+
+    @staticmethod
+    def copy_blocks(kv_caches: List[torch.Tensor], src_to_dists: torch.Tensor) -> None:
+        PagedAttention.copy_blocks(kv_caches, src_to_dists)
+
+
+@dataclass
+class B200PagedAttentionMetadata(AttentionMetadata, PagedAttentionMetadata):
+    """Field-compatible with XFormersMetadata (xformers.py:60-110) for the decode path."""
+    seq_lens: Optional[List[int]] = None
+    max_query_len: Optional[int] = None
+    max_prefill_seq_len: int = 0
+    query_start_loc: Optional[torch.Tensor] = None
+    seq_start_loc: Optional[torch.Tensor] = None
+    context_lens_tensor: Optional[torch.Tensor] = None
+    use_cuda_graph: bool = False
+
+    @property
+    def prefill_metadata(self) -> Optional["B200PagedAttentionMetadata"]:
+        if self.num_prefills == 0:
+            return None
+        return self  # prefill math is outside this path; callers only need the counts
+
+    @property
+    def decode_metadata(self) -> Optional["B200PagedAttentionMetadata"]:
+        if self.num_decode_tokens == 0:
+            return None
+        return self
+
+
+class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
+
+    def __init__(
+        self,
+        num_heads: int,
+        head_size: int,
+        scale: float,
+        num_kv_heads: Optional[int] = None,
+        alibi_slopes: Optional[List[float]] = None,
+        sliding_window: Optional[int] = None,
+        kv_cache_dtype: str = "auto",
+        blocksparse_params: Optional[Dict[str, Any]] = None,
+    ) -> None:
+        self.num_heads = num_heads
+        self.head_size = head_size
+        self.scale = float(scale)
+        self.num_kv_heads = num_heads if num_kv_heads is None else num_kv_heads
+        self.alibi_slopes = (torch.tensor(alibi_slopes, dtype=torch.float32)
+                             if alibi_slopes is not None else None)
+        self.sliding_window = sliding_window
+        self.kv_cache_dtype = kv_cache_dtype
+        self.blocksparse_params = blocksparse_params or {}
+        assert self.num_heads % self.num_kv_heads == 0
+        self.num_queries_per_kv = self.num_heads // self.num_kv_heads
+        supported = PagedAttention.get_supported_head_sizes()
+        if head_size not in supported:
+            raise ValueError(f"Head size {head_size} is not supported by PagedAttention. "
+                             f"Supported head sizes are: {supported}.")
+
+    def forward(
+        self,
+        query: torch.Tensor,
+        key: torch.Tensor,
+        value: torch.Tensor,
+        kv_cache: Optional[torch.Tensor],
+        attn_metadata: B200PagedAttentionMetadata,
+        kv_scale: float = 1.0,
+        rope_method: Literal['none', 'self_extend'] = 'none',
+        rope_cos: Optional[torch.Tensor] = None,
+        rope_sin: Optional[torch.Tensor] = None,
+        position_ids: Optional[torch.Tensor] = None,
+    ) -> torch.Tensor:
+        """query [T, Hq*D], key/value [T, Hkv*D], kv_cache [2, nb, B*Hkv*D] -> [T, Hq*D]."""
+        assert rope_method == 'none', "self-extend RoPE belongs to the HiP backend, not this path"
+        query = query.view(-1, self.num_heads, self.head_size)
+        key = key.view(-1, self.num_kv_heads, self.head_size)
+        value = value.view(-1, self.num_kv_heads, self.head_size)
+
+        key_cache = value_cache = None
+        if kv_cache is not None:
+            key_cache, value_cache = PagedAttention.split_kv_cache(kv_cache, self.num_kv_heads,
+                                                                   self.head_size)
+            PagedAttention.write_to_paged_cache(key, value, key_cache, value_cache,
+                                                attn_metadata.slot_mapping, self.kv_cache_dtype,
+                                                kv_scale)
+
+        num_prefill_tokens = attn_metadata.num_prefill_tokens
+        num_decode_tokens = attn_metadata.num_decode_tokens
+        assert key.shape[0] == num_prefill_tokens + num_decode_tokens
+        output = torch.empty_like(query)
+        decode_query = query[num_prefill_tokens:]
+
+        if decode_meta := attn_metadata.decode_metadata:
+            assert kv_cache is not None, "decode needs the paged KV cache"
+            if self.alibi_slopes is not None and self.alibi_slopes.device != query.device:
+                self.alibi_slopes = self.alibi_slopes.to(query.device)
+            bs = self.blocksparse_params
+            output[num_prefill_tokens:] = PagedAttention.forward_decode(
+                decode_query, key_cache, value_cache, decode_meta.block_tables,
+                decode_meta.seq_lens_tensor, decode_meta.max_decode_seq_len, self.kv_cache_dtype,
+                self.num_kv_heads, self.scale, self.alibi_slopes, kv_scale,
+                tp_rank=bs.get("tp_rank", 0),
+                blocksparse_local_blocks=bs.get("local_blocks", 0),
+                blocksparse_vert_stride=bs.get("vert_stride", 0),
+                blocksparse_block_size=bs.get("block_size", 64),
+                blocksparse_head_sliding_step=bs.get("head_sliding_step", 0))
+        return output.view(-1, self.num_heads * self.head_size)

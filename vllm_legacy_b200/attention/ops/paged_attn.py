@@ -1,0 +1,127 @@
+"""`PagedAttention` static helpers — the interface of the reference's
+`vllm/attention/ops/paged_attn.py:30-239` for the decode path, on top of the B200 ops.
+
+Same method names, arguments, KV-cache shape `(2, num_blocks, block_size*num_kv_heads*head_size)`,
+K view `[nb, H, D/x, B, x]` / V view `[nb, H, D, B]`, V1/V2 selection rule and scratch shapes, so the
+reference's backends (xformers.py:269-335, hip.py:166-319, blocksparse_attn.py:357-390,
+torch_sdpa.py:162-216) and cache engine (cache_engine.py:89-100) can call it unchanged.
+`forward_prefix` (Triton prefix-prefill, third-party) is outside this path.
+"""
+from dataclasses import dataclass
+from typing import List, Optional, Tuple
+
+import torch
+
+from vllm_legacy_b200 import _custom_ops as ops
+
+# Should be the same as PARTITION_SIZE in `paged_attention_v2_launcher` (paged_attn.py:10).
+_PARTITION_SIZE = 512
+
+
+@dataclass
+class PagedAttentionMetadata:
+    """Metadata for PagedAttention (paged_attn.py:13-27)."""
+    seq_lens_tensor: Optional[torch.Tensor]
+    max_decode_seq_len: int
+    block_tables: Optional[torch.Tensor]
+
+
+class PagedAttention:
+
+    @staticmethod
+    def get_supported_head_sizes() -> List[int]:
+        return [64, 80, 96, 112, 128, 192, 256]
+
+    @staticmethod
+    def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int,
+                           head_size: int) -> Tuple[int, ...]:
+        return (2, num_blocks, block_size * num_kv_heads * head_size)
+
+    @staticmethod
+    def split_kv_cache(kv_cache: torch.Tensor, num_kv_heads: int,
+                       head_size: int) -> Tuple[torch.Tensor, torch.Tensor]:
+        x = 16 // kv_cache.element_size()
+        num_blocks = kv_cache.shape[1]
+        key_cache = kv_cache[0]
+        key_cache = key_cache.view(num_blocks, num_kv_heads, head_size // x, -1, x)
+        value_cache = kv_cache[1]
+        value_cache = value_cache.view(num_blocks, num_kv_heads, head_size, -1)
+        return key_cache, value_cache
+
+    @staticmethod
+    def write_to_paged_cache(key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor,
+                             value_cache: torch.Tensor, slot_mapping: torch.Tensor,
+                             kv_cache_dtype: str, kv_scale: float) -> None:
+        ops.reshape_and_cache(key, value, key_cache, value_cache, slot_mapping.flatten(),
+                              kv_cache_dtype, kv_scale)
+
+    @staticmethod
+    def forward_decode(
+        query: torch.Tensor,
+        key_cache: torch.Tensor,
+        value_cache: torch.Tensor,
+        block_tables: torch.Tensor,
+        seq_lens: torch.Tensor,
+        max_seq_len: int,
+        kv_cache_dtype: str,
+        num_kv_heads: int,
+        scale: float,
+        alibi_slopes: Optional[torch.Tensor],
+        kv_scale: float,
+        tp_rank: int = 0,
+        blocksparse_local_blocks: int = 0,
+        blocksparse_vert_stride: int = 0,
+        blocksparse_block_size: int = 64,
+        blocksparse_head_sliding_step: int = 0,
+    ) -> torch.Tensor:
+        if blocksparse_vert_stride is not None and blocksparse_vert_stride > 1:
+            block_size = value_cache.size(-1)
+            assert (blocksparse_block_size > 0 and blocksparse_block_size % block_size == 0), \
+                (f"{blocksparse_block_size=} needs to be a multiple of"
+                 f"{block_size=} used in block_tables.")
+
+        output = torch.empty_like(query)
+        block_size = value_cache.shape[3]
+        num_seqs, num_heads, head_size = query.shape
+        max_num_partitions = (max_seq_len + _PARTITION_SIZE - 1) // _PARTITION_SIZE
+        # Reference heuristic, kept verbatim in meaning (paged_attn.py:112-121): V1 when one
+        # partition suffices or there are many (sequence, head) pairs, V2 above 8192 tokens.
+        use_v1 = (max_seq_len <= 8192 and (max_num_partitions == 1 or num_seqs * num_heads > 512))
+
+        if use_v1:
+            ops.paged_attention_v1(output, query, key_cache, value_cache, num_kv_heads, scale,
+                                   block_tables, seq_lens, block_size, max_seq_len, alibi_slopes,
+                                   kv_cache_dtype, kv_scale, tp_rank, blocksparse_local_blocks,
+                                   blocksparse_vert_stride, blocksparse_block_size,
+                                   blocksparse_head_sliding_step)
+        else:
+            assert _PARTITION_SIZE % block_size == 0
+            tmp_output = torch.empty(size=(num_seqs, num_heads, max_num_partitions, head_size),
+                                     dtype=output.dtype, device=output.device)
+            exp_sums = torch.empty(size=(num_seqs, num_heads, max_num_partitions),
+                                   dtype=torch.float32, device=output.device)
+            max_logits = torch.empty_like(exp_sums)
+            ops.paged_attention_v2(output, exp_sums, max_logits, tmp_output, query, key_cache,
+                                   value_cache, num_kv_heads, scale, block_tables, seq_lens,
+                                   block_size, max_seq_len, alibi_slopes, kv_cache_dtype, kv_scale,
+                                   tp_rank, blocksparse_local_blocks, blocksparse_vert_stride,
+                                   blocksparse_block_size, blocksparse_head_sliding_step)
+        return output
+
+    @staticmethod
+    def forward_prefix(*args, **kwargs) -> torch.Tensor:
+        raise NotImplementedError(
+            "forward_prefix (Triton context_attention_fwd, vllm/attention/ops/prefix_prefill.py) is "
+            "outside the paged-attention decode hot path; see SURVEY.md §8(f) rank 1.")
+
+    @staticmethod
+    def swap_blocks(src_kv_cache: torch.Tensor, dst_kv_cache: torch.Tensor,
+                    src_to_dst: torch.Tensor) -> None:
+        ops.swap_blocks(src_kv_cache[0], dst_kv_cache[0], src_to_dst)
+        ops.swap_blocks(src_kv_cache[1], dst_kv_cache[1], src_to_dst)
+
+    @staticmethod
+    def copy_blocks(kv_caches: List[torch.Tensor], src_to_dists: torch.Tensor) -> None:
+        key_caches = [kv_cache[0] for kv_cache in kv_caches]
+        value_caches = [kv_cache[1] for kv_cache in kv_caches]
+        ops.copy_blocks(key_caches, value_caches, src_to_dists)

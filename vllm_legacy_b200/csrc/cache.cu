@@ -1,0 +1,368 @@
+// KV-cache maintenance kernels for B200 (sm_100a): reshape_and_cache (+fp8 quantisation),
+// copy_blocks, swap_blocks, convert_fp8.  C-ABI entry points are declared in include/b200pa.h.
+//
+// Semantics follow the reference (DeepAuto-AI/vllm-legacy):
+//   reshape_and_cache  csrc/cache_kernels.cu:150-202, 241-287
+//   copy_blocks        csrc/cache_kernels.cu:68-146
+//   swap_blocks        csrc/cache_kernels.cu:25-64
+//   convert_fp8        csrc/cache_kernels.cu:347-420
+// but not their structure: 128-bit accesses where the layout allows, pointer tables passed as
+// kernel parameters (no per-call H2D copy / sync), swap runs merged into large async copies.
+#include <algorithm>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace b200pa {
+
+thread_local int g_last_cuda_error = 0;
+thread_local const char* g_last_attention_path = "";
+thread_local int g_last_attention_partitions = 0;
+
+// =============================================================================================
+// reshape_and_cache
+// =============================================================================================
+
+template <typename T, int KV>
+struct CacheStore {
+  using type = uint8_t;
+  static __device__ __forceinline__ uint8_t cvt(T v, float scale) { return fp8_quant<KV, T>(v, scale); }
+};
+template <typename T>
+struct CacheStore<T, B200PA_KV_AUTO> {
+  using type = T;
+  static __device__ __forceinline__ T cvt(T v, float) { return v; }
+};
+
+// Generic path: any x, any alignment.  One CTA per token, one element per thread-iteration.
+// Index math as cache_kernels.cu:169-200.
+template <typename T, int KV>
+__global__ void reshape_and_cache_scalar_kernel(const T* __restrict__ key, const T* __restrict__ value,
+                                                typename CacheStore<T, KV>::type* __restrict__ key_cache,
+                                                typename CacheStore<T, KV>::type* __restrict__ value_cache,
+                                                const int64_t* __restrict__ slot_mapping,
+                                                int64_t key_stride, int64_t value_stride, int num_heads,
+                                                int head_size, int block_size, int x, float kv_scale) {
+  const int64_t token = blockIdx.x;
+  const int64_t slot = slot_mapping[token];
+  if (slot < 0) return;  // padding token
+  const int64_t block_idx = slot / block_size;
+  const int64_t block_off = slot % block_size;
+  const int n = num_heads * head_size;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int h = i / head_size;
+    const int d = i % head_size;
+    const int64_t kdst = block_idx * num_heads * (head_size / x) * block_size * x +
+                         (int64_t)h * (head_size / x) * block_size * x + (int64_t)(d / x) * block_size * x +
+                         block_off * x + (d % x);
+    const int64_t vdst = block_idx * num_heads * head_size * block_size + (int64_t)h * head_size * block_size +
+                         (int64_t)d * block_size + block_off;
+    key_cache[kdst] = CacheStore<T, KV>::cvt(key[token * key_stride + i], kv_scale);
+    value_cache[vdst] = CacheStore<T, KV>::cvt(value[token * value_stride + i], kv_scale);
+  }
+}
+
+// Vector path: x * sizeof(cache_t) == 16 and 16-byte aligned sources.  Each thread-iteration
+// moves one x-group of K with 128-bit loads and ONE 128-bit store (the K layout keeps the x
+// elements of a token contiguous), and x elements of V with 128-bit loads and x element stores
+// (the V layout is token-minor, so one token's elements are block_size apart by construction).
+template <typename T, int KV>
+__global__ void reshape_and_cache_vec_kernel(const T* __restrict__ key, const T* __restrict__ value,
+                                             typename CacheStore<T, KV>::type* __restrict__ key_cache,
+                                             typename CacheStore<T, KV>::type* __restrict__ value_cache,
+                                             const int64_t* __restrict__ slot_mapping, int64_t key_stride,
+                                             int64_t value_stride, int num_heads, int head_size,
+                                             int block_size, float kv_scale) {
+  using CT = typename CacheStore<T, KV>::type;
+  constexpr int X = 16 / sizeof(CT);                // elements per K group
+  constexpr int SRC_VECS = X * sizeof(T) / 16;      // int4 loads per group
+  constexpr int EPV = 16 / sizeof(T);               // source elements per int4
+  const int64_t token = blockIdx.x;
+  const int64_t slot = slot_mapping[token];
+  if (slot < 0) return;
+  const int64_t block_idx = slot / block_size;
+  const int block_off = (int)(slot % block_size);
+  const int groups_per_head = head_size / X;
+  const int n_groups = num_heads * groups_per_head;
+  const T* ksrc = key + token * key_stride;
+  const T* vsrc = value + token * value_stride;
+  CT* kblk = key_cache + block_idx * (int64_t)num_heads * head_size * block_size;
+  CT* vblk = value_cache + block_idx * (int64_t)num_heads * head_size * block_size;
+
+  for (int g = threadIdx.x; g < n_groups; g += blockDim.x) {
+    const int h = g / groups_per_head;
+    const int dx = g % groups_per_head;
+    const int e0 = h * head_size + dx * X;  // first source element of the group
+    union { int4 v[SRC_VECS]; T e[X]; } kin, vin;
+#pragma unroll
+    for (int j = 0; j < SRC_VECS; ++j) {
+      kin.v[j] = ld_nc_v4(ksrc + e0 + j * EPV);
+      vin.v[j] = ld_nc_v4(vsrc + e0 + j * EPV);
+    }
+    union { int4 v; CT e[X]; } kout;
+#pragma unroll
+    for (int j = 0; j < X; ++j) kout.e[j] = CacheStore<T, KV>::cvt(kin.e[j], kv_scale);
+    CT* kdst = kblk + ((int64_t)(h * groups_per_head + dx) * block_size + block_off) * X;
+    *reinterpret_cast<int4*>(kdst) = kout.v;
+    CT* vdst = vblk + ((int64_t)h * head_size + dx * X) * block_size + block_off;
+#pragma unroll
+    for (int j = 0; j < X; ++j) vdst[(int64_t)j * block_size] = CacheStore<T, KV>::cvt(vin.e[j], kv_scale);
+  }
+}
+
+template <typename T, int KV>
+static int launch_reshape(const b200pa_reshape_params_t* p, cudaStream_t stream) {
+  using CT = typename CacheStore<T, KV>::type;
+  if (p->num_tokens == 0) return B200PA_OK;
+  const int n = p->num_heads * p->head_size;
+  constexpr int X = 16 / sizeof(CT);
+  const bool vec_ok = p->x == X && p->head_size % X == 0 &&
+                      (reinterpret_cast<uintptr_t>(p->key) % 16 == 0) &&
+                      (reinterpret_cast<uintptr_t>(p->value) % 16 == 0) &&
+                      (reinterpret_cast<uintptr_t>(p->key_cache) % 16 == 0) &&
+                      (p->key_stride * sizeof(T)) % 16 == 0 && (p->value_stride * sizeof(T)) % 16 == 0;
+  dim3 grid(p->num_tokens);
+  if (vec_ok) {
+    int threads = std::min(std::max(n / X, 32), 256);
+    threads = (threads + 31) / 32 * 32;
+    reshape_and_cache_vec_kernel<T, KV><<<grid, threads, 0, stream>>>(
+        static_cast<const T*>(p->key), static_cast<const T*>(p->value), static_cast<CT*>(p->key_cache),
+        static_cast<CT*>(p->value_cache), p->slot_mapping, p->key_stride, p->value_stride, p->num_heads,
+        p->head_size, p->block_size, p->kv_scale);
+  } else {
+    int threads = std::min(n, 512);
+    reshape_and_cache_scalar_kernel<T, KV><<<grid, threads, 0, stream>>>(
+        static_cast<const T*>(p->key), static_cast<const T*>(p->value), static_cast<CT*>(p->key_cache),
+        static_cast<CT*>(p->value_cache), p->slot_mapping, p->key_stride, p->value_stride, p->num_heads,
+        p->head_size, p->block_size, p->x, p->kv_scale);
+  }
+  B200PA_CUDA_CHECK(cudaGetLastError());
+  return B200PA_OK;
+}
+
+template <int KV>
+static int dispatch_reshape_dtype(const b200pa_reshape_params_t* p, cudaStream_t stream) {
+  switch (p->dtype) {
+    case B200PA_F16: return launch_reshape<__half, KV>(p, stream);
+    case B200PA_BF16: return launch_reshape<__nv_bfloat16, KV>(p, stream);
+    case B200PA_F32: return launch_reshape<float, KV>(p, stream);
+    default: return B200PA_ERR_INPUT_DTYPE;
+  }
+}
+
+// =============================================================================================
+// copy_blocks
+// =============================================================================================
+
+constexpr int kMaxLayersPerLaunch = 120;  // 2 * 120 * 8 B = 1920 B of kernel parameters
+
+struct LayerPtrs {
+  char* k[kMaxLayersPerLaunch];
+  char* v[kMaxLayersPerLaunch];
+};
+
+// One CTA per (layer, pair): K block then V block, 128-bit accesses, 4 loads in flight per thread.
+__global__ void copy_blocks_vec_kernel(const __grid_constant__ LayerPtrs ptrs,
+                                       const int64_t* __restrict__ block_mapping, int64_t vecs_per_block) {
+  const int layer = blockIdx.x;
+  const int64_t pair = blockIdx.y;
+  const int64_t src = block_mapping[2 * pair];
+  const int64_t dst = block_mapping[2 * pair + 1];
+#pragma unroll
+  for (int kv = 0; kv < 2; ++kv) {
+    char* base = kv == 0 ? ptrs.k[layer] : ptrs.v[layer];
+    const int4* s = reinterpret_cast<const int4*>(base) + src * vecs_per_block;
+    int4* d = reinterpret_cast<int4*>(base) + dst * vecs_per_block;
+    int64_t i = threadIdx.x;
+    for (; i + 3 * (int64_t)blockDim.x < vecs_per_block; i += 4 * (int64_t)blockDim.x) {
+      int4 a = ld_nc_v4(s + i), b = ld_nc_v4(s + i + blockDim.x), c = ld_nc_v4(s + i + 2 * blockDim.x),
+           e = ld_nc_v4(s + i + 3 * blockDim.x);
+      st_na_v4(d + i, a);
+      st_na_v4(d + i + blockDim.x, b);
+      st_na_v4(d + i + 2 * blockDim.x, c);
+      st_na_v4(d + i + 3 * blockDim.x, e);
+    }
+    for (; i < vecs_per_block; i += blockDim.x) st_na_v4(d + i, ld_nc_v4(s + i));
+  }
+}
+
+__global__ void copy_blocks_byte_kernel(const __grid_constant__ LayerPtrs ptrs,
+                                        const int64_t* __restrict__ block_mapping, int64_t block_bytes) {
+  const int layer = blockIdx.x;
+  const int64_t pair = blockIdx.y;
+  const int64_t src = block_mapping[2 * pair];
+  const int64_t dst = block_mapping[2 * pair + 1];
+  for (int kv = 0; kv < 2; ++kv) {
+    char* base = kv == 0 ? ptrs.k[layer] : ptrs.v[layer];
+    const char* s = base + src * block_bytes;
+    char* d = base + dst * block_bytes;
+    for (int64_t i = threadIdx.x; i < block_bytes; i += blockDim.x) d[i] = s[i];
+  }
+}
+
+// =============================================================================================
+// convert_fp8
+// =============================================================================================
+
+template <typename T, int KV>
+__global__ void fp8_quant_kernel(uint8_t* __restrict__ dst, const T* __restrict__ src, int64_t n, float scale) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = fp8_quant<KV, T>(src[i], scale);
+}
+template <typename T, int KV>
+__global__ void fp8_dequant_kernel(T* __restrict__ dst, const uint8_t* __restrict__ src, int64_t n, float scale) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = fp8_dequant<KV, T>(src[i], scale);
+}
+
+template <int KV>
+static int launch_convert(void* dst, const void* src, int64_t n, int dst_dtype, int src_dtype, float scale,
+                          cudaStream_t stream) {
+  const int threads = 256;
+  const int64_t want = (n + threads - 1) / threads;
+  const int blocks = (int)std::min<int64_t>(want, 148 * 32);
+  if (dst_dtype == B200PA_U8) {
+    uint8_t* d = static_cast<uint8_t*>(dst);
+    switch (src_dtype) {
+      case B200PA_F16: fp8_quant_kernel<__half, KV><<<blocks, threads, 0, stream>>>(d, (const __half*)src, n, scale); break;
+      case B200PA_BF16: fp8_quant_kernel<__nv_bfloat16, KV><<<blocks, threads, 0, stream>>>(d, (const __nv_bfloat16*)src, n, scale); break;
+      case B200PA_F32: fp8_quant_kernel<float, KV><<<blocks, threads, 0, stream>>>(d, (const float*)src, n, scale); break;
+      default: return B200PA_ERR_INPUT_DTYPE;
+    }
+  } else if (src_dtype == B200PA_U8) {
+    const uint8_t* s = static_cast<const uint8_t*>(src);
+    switch (dst_dtype) {
+      case B200PA_F16: fp8_dequant_kernel<__half, KV><<<blocks, threads, 0, stream>>>((__half*)dst, s, n, scale); break;
+      case B200PA_BF16: fp8_dequant_kernel<__nv_bfloat16, KV><<<blocks, threads, 0, stream>>>((__nv_bfloat16*)dst, s, n, scale); break;
+      case B200PA_F32: fp8_dequant_kernel<float, KV><<<blocks, threads, 0, stream>>>((float*)dst, s, n, scale); break;
+      default: return B200PA_ERR_INPUT_DTYPE;
+    }
+  } else {
+    return B200PA_ERR_INPUT_DTYPE;
+  }
+  B200PA_CUDA_CHECK(cudaGetLastError());
+  return B200PA_OK;
+}
+
+}  // namespace b200pa
+
+// =============================================================================================
+// C-ABI
+// =============================================================================================
+using namespace b200pa;
+
+extern "C" int b200pa_reshape_and_cache(const b200pa_reshape_params_t* p, b200pa_stream_t stream) {
+  if (!p) return B200PA_ERR_INVALID_ARG;
+  if (p->num_tokens < 0 || p->num_heads <= 0 || p->head_size <= 0 || p->block_size <= 0 || p->x <= 0 ||
+      p->head_size % p->x != 0)
+    return B200PA_ERR_INVALID_ARG;
+  if (p->num_tokens > 0 && (!p->key || !p->value || !p->key_cache || !p->value_cache || !p->slot_mapping))
+    return B200PA_ERR_INVALID_ARG;
+  switch (p->kv_dtype) {
+    case B200PA_KV_AUTO: return dispatch_reshape_dtype<B200PA_KV_AUTO>(p, stream);
+    case B200PA_KV_FP8_E4M3: return dispatch_reshape_dtype<B200PA_KV_FP8_E4M3>(p, stream);
+    case B200PA_KV_FP8_E5M2: return dispatch_reshape_dtype<B200PA_KV_FP8_E5M2>(p, stream);
+    default: return B200PA_ERR_KV_DTYPE;
+  }
+}
+
+extern "C" int b200pa_copy_blocks(void* const* key_cache_ptrs, void* const* value_cache_ptrs, int32_t num_layers,
+                                  const int64_t* block_mapping, int64_t num_pairs, int64_t block_bytes,
+                                  b200pa_stream_t stream) {
+  if (num_layers < 0 || num_pairs < 0 || block_bytes < 0) return B200PA_ERR_INVALID_ARG;
+  if (num_layers == 0 || num_pairs == 0 || block_bytes == 0) return B200PA_OK;
+  if (!key_cache_ptrs || !value_cache_ptrs || !block_mapping) return B200PA_ERR_INVALID_ARG;
+  bool aligned = block_bytes % 16 == 0;
+  for (int l = 0; l < num_layers && aligned; ++l)
+    aligned = reinterpret_cast<uintptr_t>(key_cache_ptrs[l]) % 16 == 0 &&
+              reinterpret_cast<uintptr_t>(value_cache_ptrs[l]) % 16 == 0;
+  for (int l0 = 0; l0 < num_layers; l0 += kMaxLayersPerLaunch) {
+    const int nl = std::min(kMaxLayersPerLaunch, num_layers - l0);
+    LayerPtrs ptrs;
+    std::memset(&ptrs, 0, sizeof(ptrs));
+    for (int l = 0; l < nl; ++l) {
+      ptrs.k[l] = static_cast<char*>(key_cache_ptrs[l0 + l]);
+      ptrs.v[l] = static_cast<char*>(value_cache_ptrs[l0 + l]);
+    }
+    // gridDim.y is limited to 65535
+    for (int64_t p0 = 0; p0 < num_pairs; p0 += 65535) {
+      const int np = (int)std::min<int64_t>(65535, num_pairs - p0);
+      dim3 grid(nl, np);
+      if (aligned) {
+        const int64_t vecs = block_bytes / 16;
+        const int threads = (int)std::min<int64_t>(256, std::max<int64_t>(32, (vecs + 3) / 4 / 32 * 32));
+        copy_blocks_vec_kernel<<<grid, threads, 0, stream>>>(ptrs, block_mapping + 2 * p0, vecs);
+      } else {
+        copy_blocks_byte_kernel<<<grid, 256, 0, stream>>>(ptrs, block_mapping + 2 * p0, block_bytes);
+      }
+      B200PA_CUDA_CHECK(cudaGetLastError());
+    }
+  }
+  return B200PA_OK;
+}
+
+extern "C" int b200pa_swap_blocks(const void* src, void* dst, const int64_t* block_mapping_host, int64_t num_pairs,
+                                  int64_t block_bytes, int32_t kind, b200pa_stream_t stream) {
+  if (num_pairs < 0 || block_bytes < 0) return B200PA_ERR_INVALID_ARG;
+  if (num_pairs == 0 || block_bytes == 0) return B200PA_OK;
+  if (!src || !dst || !block_mapping_host) return B200PA_ERR_INVALID_ARG;
+  cudaMemcpyKind k;
+  switch (kind) {
+    case B200PA_D2D: k = cudaMemcpyDeviceToDevice; break;
+    case B200PA_D2H: k = cudaMemcpyDeviceToHost; break;
+    case B200PA_H2D: k = cudaMemcpyHostToDevice; break;
+    default: return B200PA_ERR_DEVICE_COMBINATION;
+  }
+  const char* s = static_cast<const char*>(src);
+  char* d = static_cast<char*>(dst);
+  // Merge runs (src+1 -> dst+1) into one copy: the scheduler hands out mostly-contiguous
+  // block ranges, and one large PCIe transfer beats many 32 KiB ones.
+  int64_t i = 0;
+  while (i < num_pairs) {
+    const int64_t s0 = block_mapping_host[2 * i], d0 = block_mapping_host[2 * i + 1];
+    int64_t run = 1;
+    while (i + run < num_pairs && block_mapping_host[2 * (i + run)] == s0 + run &&
+           block_mapping_host[2 * (i + run) + 1] == d0 + run)
+      ++run;
+    B200PA_CUDA_CHECK(cudaMemcpyAsync(d + d0 * block_bytes, s + s0 * block_bytes, (size_t)(run * block_bytes), k, stream));
+    i += run;
+  }
+  return B200PA_OK;
+}
+
+extern "C" int b200pa_convert_fp8(void* dst, const void* src, int64_t numel, int32_t dst_dtype, int32_t src_dtype,
+                                  float scale, int32_t kv_dtype, b200pa_stream_t stream) {
+  if (numel < 0) return B200PA_ERR_INVALID_ARG;
+  if (numel == 0) return B200PA_OK;
+  if (!dst || !src) return B200PA_ERR_INVALID_ARG;
+  switch (kv_dtype) {
+    case B200PA_KV_FP8_E4M3: return launch_convert<B200PA_KV_FP8_E4M3>(dst, src, numel, dst_dtype, src_dtype, scale, stream);
+    case B200PA_KV_FP8_E5M2: return launch_convert<B200PA_KV_FP8_E5M2>(dst, src, numel, dst_dtype, src_dtype, scale, stream);
+    default: return B200PA_ERR_KV_DTYPE;  // "auto" is not convertible (reference: assert(false) path)
+  }
+}
+
+extern "C" int b200pa_get_max_shared_memory_per_block_device_attribute(int32_t device_id) {
+  int v = 0;
+  if (cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, device_id) != cudaSuccess) return -1;
+  return v;
+}
+
+extern "C" int b200pa_abi_version(void) { return B200PA_ABI_VERSION; }
+extern "C" int b200pa_last_cuda_error(void) { return g_last_cuda_error; }
+extern "C" const char* b200pa_last_attention_path(void) { return g_last_attention_path; }
+extern "C" int b200pa_last_attention_partitions(void) { return g_last_attention_partitions; }
+
+extern "C" const char* b200pa_status_string(int status) {
+  switch (status) {
+    case B200PA_OK: return "ok";
+    case B200PA_ERR_HEAD_SIZE: return "Unsupported head size: ";
+    case B200PA_ERR_BLOCK_SIZE: return "Unsupported block size: ";
+    case B200PA_ERR_KV_DTYPE: return "Unsupported data type of kv cache: ";
+    case B200PA_ERR_INPUT_DTYPE: return "Unsupported input type of kv cache: ";
+    case B200PA_ERR_INVALID_ARG: return "invalid argument";
+    case B200PA_ERR_CUDA: return "CUDA error";
+    case B200PA_ERR_DEVICE_COMBINATION: return "Invalid device combination";
+    default: return "unknown status";
+  }
+}
