@@ -65,22 +65,19 @@ def _attn(ops, version, q, kc, vc, Hkv, scale, bt, sl, B, L, kvd, kv_scale=1.0):
 def _spot_check(ops, out, q, kc, vc, bt, sl, scale, Hkv, kvd, rows, atol, kv_scale=1.0):
     S, Hq, D = q.shape
     rows = torch.tensor(rows, device=DEV)
+    bt_rows = bt[rows]
     if kvd == "fp8":
-        # dequantise only the blocks these rows touch
-        used = torch.unique(bt[rows].flatten().long())
-        kd = torch.zeros(kc.shape[0], *kc.shape[1:], dtype=q.dtype, device=DEV) if kc.shape[0] < 70000 else None
-        assert kd is not None
-        vd = torch.zeros(vc.shape, dtype=q.dtype, device=DEV)
-        ku = torch.empty(kc[used].shape, dtype=q.dtype, device=DEV)
-        vu = torch.empty(vc[used].shape, dtype=q.dtype, device=DEV)
-        ops.convert_fp8(ku, kc[used].contiguous(), kv_scale)
-        ops.convert_fp8(vu, vc[used].contiguous(), kv_scale)
-        kd[used] = ku
-        vd[used] = vu
+        # dequantise only the blocks these rows touch, compacted, and remap the table onto them
+        used, inv = torch.unique(bt_rows.flatten().long(), return_inverse=True)
+        kd = torch.empty(kc[used].shape, dtype=q.dtype, device=DEV)
+        vd = torch.empty(vc[used].shape, dtype=q.dtype, device=DEV)
+        ops.convert_fp8(kd, kc[used].contiguous(), kv_scale)
+        ops.convert_fp8(vd, vc[used].contiguous(), kv_scale)
+        bt_rows = inv.view(bt_rows.shape).to(torch.int32)
     else:
         kd, vd = kc, vc
     want = torch.empty(len(rows), Hq, D, dtype=q.dtype, device=DEV)
-    helpers.ref_single_query_cached_kv_attention(want, q[rows], Hq // Hkv, kd, vd, bt[rows], sl[rows], scale, None)
+    helpers.ref_single_query_cached_kv_attention(want, q[rows], Hq // Hkv, kd, vd, bt_rows, sl[rows], scale, None)
     got = out[rows]
     assert torch.allclose(got.float(), want.float(), atol=atol, rtol=1e-2), (got.float() - want.float()).abs().max()
 
