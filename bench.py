@@ -266,6 +266,11 @@ def cpu_reference_run(total_budget_s, steps, warmup):
     """Times paged_attention_v2 of the CPU reference on a bounded sample of CFG (fewer sequences, same heads /
     context / block size / dtype, distinct physical blocks).  Returns (GB/s, description dict)."""
     kind, impl = _cpu_reference_impl()
+    # all host threads this process may use (torchrun exports OMP_NUM_THREADS=1; undo that for the CPU arm)
+    try:
+        torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
+    except Exception:  # noqa: BLE001
+        pass
     cfg = dict(CFG)
     L, Hq, Hkv, D, B = (cfg[k] for k in ("ctx", "num_heads", "num_kv_heads", "head_size", "block_size"))
     cores = torch.get_num_threads() if kind == "reference" else 1
