@@ -93,6 +93,41 @@ def test_reshape_and_cache_scalar_path_and_empty(ops, oracle):
     assert torch.equal(_bits(kc_d.cpu()), _bits(kc))
 
 
+@pytest.mark.parametrize("shape", [(8, 128, 16), (3, 80, 32), (40, 64, 8), (5, 256, 16), (12, 192, 16)])
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("kv_cache_dtype", ["auto", "fp8"])
+@pytest.mark.parametrize("consecutive", [True, False])
+@torch.inference_mode()
+def test_reshape_and_cache_tile_path(ops, oracle, shape, dtype, kv_cache_dtype, consecutive):
+    """num_tokens >= 512 takes the shared-memory tile kernel (prefill): prompt-like consecutive slots starting
+    at an arbitrary offset inside a block, or fully random slots, with padding tokens and a ragged last tile."""
+    num_heads, head_size, block_size = shape
+    random.seed(1)
+    torch.manual_seed(1)
+    T, num_blocks = 1000 + 7, 160
+    if consecutive:
+        start = 5  # not block aligned
+        slots = torch.arange(start, start + T, dtype=torch.long)
+    else:
+        slots = torch.tensor(random.sample(range(num_blocks * block_size), T), dtype=torch.long)
+    slots[17] = -1
+    slots[T - 1] = -1
+    qkv = torch.randn(T, 3, num_heads, head_size, dtype=dtype)
+    _, key, value = qkv.unbind(dim=1)
+    nb = max(num_blocks, (T + 5) // block_size + 2)
+    kcs, vcs = helpers.create_kv_caches_with_random(nb, block_size, 1, num_heads, head_size, kv_cache_dtype, dtype, 1,
+                                                    "cpu", oracle.convert_fp8)
+    kc_ref, vc_ref = kcs[0], vcs[0]
+    kc, vc = kc_ref.to(DEV), vc_ref.to(DEV)
+    qkv_d = qkv.to(DEV)
+    _, key_d, value_d = qkv_d.unbind(dim=1)
+    kv_scale = 1.0 if kv_cache_dtype == "auto" else 0.25
+    ops.reshape_and_cache(key_d, value_d, kc, vc, slots.to(DEV), kv_cache_dtype, kv_scale)
+    oracle.reshape_and_cache(key, value, kc_ref, vc_ref, slots, kv_cache_dtype, kv_scale)
+    assert torch.equal(_bits(kc.cpu()), _bits(kc_ref))
+    assert torch.equal(_bits(vc.cpu()), _bits(vc_ref))
+
+
 def test_reshape_and_cache_bad_kv_dtype(ops):
     k = torch.zeros(1, 2, 64, dtype=torch.half, device=DEV)
     kc = torch.zeros(2, 2, 8, 16, 8, dtype=torch.half, device=DEV)

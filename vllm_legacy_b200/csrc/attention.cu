@@ -72,6 +72,7 @@ static int run_attention(const b200pa_attn_params_t* a, bool allow_split, cudaSt
   kp.bs_block_size = a->blocksparse_block_size;
   kp.bs_head_sliding_step = a->blocksparse_head_sliding_step;
   kp.num_stages = env_int("B200PA_STAGES", 0);
+  kp.flags = env_int("B200PA_EVICT_NORMAL", 0) ? 1 : 0;
 
   const bool blocksparse = a->blocksparse_vert_stride > 1;
   if (blocksparse && (a->blocksparse_block_size <= 0 || a->blocksparse_block_size % a->block_size != 0))

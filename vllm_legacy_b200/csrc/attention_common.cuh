@@ -34,6 +34,7 @@ struct AttnKernelParams {
   int num_parts;       // gridDim.z; 1 => write `out` directly
   int scratch_parts;   // partition stride of the scratch buffers (caller's max_num_partitions)
   int num_stages;      // mma kernel: TMA ring depth per warp
+  int flags;           // bit 0: L2 evict_normal instead of evict_first for the KV stream (tuning knob)
   float scale;
   float kv_scale;
   int tp_rank;

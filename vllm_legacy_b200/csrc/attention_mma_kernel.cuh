@@ -71,6 +71,11 @@ __device__ __forceinline__ uint64_t l2_evict_first_policy() {
   asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
   return pol;
 }
+__device__ __forceinline__ uint64_t l2_evict_normal_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
 // TMA 1-D bulk copy global -> shared, completion on an mbarrier (SASS: UBLKCP).
 __device__ __forceinline__ void tma_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar,
                                              uint64_t policy) {
@@ -133,11 +138,20 @@ __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
-// two fp8 bytes (low 16 bits of `w`) -> packed half2, exact (cvt.rn.f16x2.e4m3x2 / e5m2x2)
+// four fp8 bytes -> two packed half2 (bytes 0,1 -> lo; bytes 2,3 -> hi), exact.  Written in PTX so that
+// ptxas folds the 16-bit half selection into the convert (SASS: F2FP.F16.E4M3.UNPACK_B Rd, Rs.H0/.H1)
+// instead of the byte shuffles the cuda_fp8.h struct round trip produces.
 template <int KV>
-__device__ __forceinline__ uint32_t fp8x2_to_half2(uint32_t w) {
-  __half2_raw h = __nv_cvt_fp8x2_to_halfraw2(static_cast<__nv_fp8x2_storage_t>(w & 0xffffu), fp8_interp<KV>());
-  return static_cast<uint32_t>(h.x) | (static_cast<uint32_t>(h.y) << 16);
+__device__ __forceinline__ void fp8x4_to_half2x2(uint32_t w, uint32_t& lo, uint32_t& hi) {
+  if constexpr (KV == B200PA_KV_FP8_E5M2) {
+    asm("{\n.reg .b16 l, h;\nmov.b32 {l, h}, %2;\ncvt.rn.f16x2.e5m2x2 %0, l;\ncvt.rn.f16x2.e5m2x2 %1, h;\n}"
+        : "=r"(lo), "=r"(hi)
+        : "r"(w));
+  } else {
+    asm("{\n.reg .b16 l, h;\nmov.b32 {l, h}, %2;\ncvt.rn.f16x2.e4m3x2 %0, l;\ncvt.rn.f16x2.e4m3x2 %1, h;\n}"
+        : "=r"(lo), "=r"(hi)
+        : "r"(w));
+  }
 }
 
 // 2^x, one MUFU.EX2 (inputs here are <= 0 or the finite kNegBig sentinel; ftz is harmless)
@@ -226,7 +240,7 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
   if (lane == 0) {
     for (int s = 0; s < NST; ++s) mbar_init(bar_base + s * 8, 1);
     fence_proxy_async_smem();
-    policy = l2_evict_first_policy();
+    policy = (p.flags & 1) ? l2_evict_normal_policy() : l2_evict_first_policy();
     const int n0 = min(NST, my_n);
     for (int i = 0; i < n0; ++i) {
       const int64_t phys = block_table[i * kMmaWarps];
@@ -362,8 +376,8 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
           if (ks < KS) {
 #pragma unroll
             for (int nt = 0; nt < 2; ++nt) {
-              const uint32_t w = r[2 * h + nt];
-              const uint32_t b0 = fp8x2_to_half2<KV>(w), b1 = fp8x2_to_half2<KV>(w >> 16);
+              uint32_t b0, b1;
+              fp8x4_to_half2x2<KV>(r[2 * h + nt], b0, b1);
               if constexpr (NG == 2)
                 mma_16816<MT>(sacc[nt], qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], b0, b1);
               else
@@ -379,7 +393,8 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
         ldmatrix_x4(kb + ks * UNIT + koff[0], r[0], r[1], r[2], r[3]);
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt) {
-          const uint32_t b0 = fp8x2_to_half2<KV>(r[nt]), b1 = fp8x2_to_half2<KV>(r[nt] >> 16);
+          uint32_t b0, b1;
+          fp8x4_to_half2x2<KV>(r[nt], b0, b1);
           if constexpr (NG == 2)
             mma_16816<MT>(sacc[nt], qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], b0, b1);
           else
@@ -485,11 +500,11 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
           va[h][0] = v.x; va[h][1] = v.y; va[h][2] = v.z; va[h][3] = v.w;
         } else if constexpr (FP8 && B == 16) {
           const uint32_t v = lds32(addr);
-          va[h][0] = fp8x2_to_half2<KV>(v); va[h][1] = fp8x2_to_half2<KV>(v >> 16);
+          fp8x4_to_half2x2<KV>(v, va[h][0], va[h][1]);
         } else {
           const uint2 v = lds64(addr);
-          va[h][0] = fp8x2_to_half2<KV>(v.x); va[h][1] = fp8x2_to_half2<KV>(v.x >> 16);
-          va[h][2] = fp8x2_to_half2<KV>(v.y); va[h][3] = fp8x2_to_half2<KV>(v.y >> 16);
+          fp8x4_to_half2x2<KV>(v.x, va[h][0], va[h][1]);
+          fp8x4_to_half2x2<KV>(v.y, va[h][2], va[h][3]);
         }
         if (partial) {
 #pragma unroll

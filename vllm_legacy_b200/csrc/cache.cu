@@ -110,6 +110,102 @@ __global__ void reshape_and_cache_vec_kernel(const T* __restrict__ key, const T*
   }
 }
 
+
+// Tile path (prefill / chunked prefill, num_tokens >= kTileMinTokens): one CTA stages TT = 16
+// consecutive tokens x (heads_per_cta * D) elements of K and V in shared memory (coalesced 128-bit row
+// reads, converted to the cache type on the way in), then writes them out with the TOKEN index fastest
+// across lanes.  When the tile's slots are consecutive inside a block — the normal case for a prompt —
+// a warp's K stores cover 512 contiguous bytes ([dx][o][x]: 16 tokens x 16 B, next dx right behind) and
+// its V stores fill whole 32-byte sectors ([d][o] rows), instead of one 16-B / 2-B piece per sector.
+// Arbitrary slot mappings stay correct (the mapping only changes which addresses coalesce).
+// Shared rows are padded (K: +16 B, V: +4 B) so both transposed reads are bank-conflict free.
+constexpr int kTileTokens = 16;
+constexpr int kTileMinTokens = 512;
+constexpr int kTileThreads = 256;
+
+template <typename T, int KV>
+__global__ void __launch_bounds__(kTileThreads)
+    reshape_and_cache_tile_kernel(const T* __restrict__ key, const T* __restrict__ value,
+                                  typename CacheStore<T, KV>::type* __restrict__ key_cache,
+                                  typename CacheStore<T, KV>::type* __restrict__ value_cache,
+                                  const int64_t* __restrict__ slot_mapping, int64_t key_stride, int64_t value_stride,
+                                  int num_tokens, int num_heads, int head_size, int block_size, int heads_per_cta,
+                                  float kv_scale) {
+  using CT = typename CacheStore<T, KV>::type;
+  constexpr int TT = kTileTokens;
+  constexpr int X = 16 / sizeof(CT);        // cache elements per 16-byte K group
+  constexpr int EPV = 16 / sizeof(T);       // source elements per 128-bit load
+  constexpr int VPAD = 4 / sizeof(CT);      // one 32-bit word of padding per V row
+  extern __shared__ __align__(16) unsigned char tile_smem[];
+  __shared__ int64_t slot_s[TT];
+
+  const int t0 = blockIdx.x * TT;
+  const int h0 = blockIdx.y * heads_per_cta;
+  const int nh = min(heads_per_cta, num_heads - h0);
+  const int n = nh * head_size;             // elements per token handled here
+  const int rsk = heads_per_cta * head_size + X;     // K row stride (elements): 16-byte aligned rows
+  const int rsv = heads_per_cta * head_size + VPAD;  // V row stride (elements): odd number of words
+  CT* ks = reinterpret_cast<CT*>(tile_smem);
+  CT* vs = ks + TT * rsk;
+
+  if (threadIdx.x < TT) {
+    const int t = t0 + threadIdx.x;
+    slot_s[threadIdx.x] = t < num_tokens ? slot_mapping[t] : -1;
+  }
+  __syncthreads();
+
+  // ---- stage: coalesced 128-bit row reads -> cache type -> shared ------------------------------------
+  const int vec_per_tok = n / EPV;
+  for (int idx = threadIdx.x; idx < TT * vec_per_tok; idx += kTileThreads) {
+    const int j = idx / vec_per_tok;
+    const int c = idx - j * vec_per_tok;
+    if (slot_s[j] < 0) continue;
+    const int64_t t = t0 + j;
+    union { int4 v; T e[EPV]; } kin, vin;
+    kin.v = ld_nc_v4(key + t * key_stride + (int64_t)h0 * head_size + c * EPV);
+    vin.v = ld_nc_v4(value + t * value_stride + (int64_t)h0 * head_size + c * EPV);
+    union { CT e[EPV]; uint32_t w[EPV * sizeof(CT) / 4]; } ko, vo;
+#pragma unroll
+    for (int e = 0; e < EPV; ++e) {
+      ko.e[e] = CacheStore<T, KV>::cvt(kin.e[e], kv_scale);
+      vo.e[e] = CacheStore<T, KV>::cvt(vin.e[e], kv_scale);
+    }
+    uint32_t* kd = reinterpret_cast<uint32_t*>(ks + j * rsk + c * EPV);
+    uint32_t* vd = reinterpret_cast<uint32_t*>(vs + j * rsv + c * EPV);
+#pragma unroll
+    for (int w = 0; w < (int)(EPV * sizeof(CT) / 4); ++w) {
+      kd[w] = ko.w[w];
+      vd[w] = vo.w[w];
+    }
+  }
+  __syncthreads();
+
+  // ---- write out: thread = (token j = tid % TT, row lane = tid / TT); token fastest across lanes -------
+  // dst(K) = kc + b*H*D*B + ((h*G + dx)*B + o)*X with h*G + dx = h0*G + u   (G = D/X groups per head)
+  // dst(V) = vc + b*H*D*B + (h*D + d)*B + o      with h*D + d  = h0*D + e
+  // so each thread needs its token's (b, o) once and then walks u / e with a constant stride.
+  const int j = threadIdx.x % TT;
+  const int r0 = threadIdx.x / TT;
+  constexpr int RL = kTileThreads / TT;  // row lanes
+  const int64_t slot = slot_s[j];
+  if (slot < 0) return;
+  const int64_t b = slot / block_size;
+  const int o = (int)(slot - b * block_size);
+  const int64_t blk_elems = (int64_t)num_heads * head_size * block_size;
+  const int groups_per_head = head_size / X;
+  CT* kdst = key_cache + b * blk_elems + ((int64_t)h0 * groups_per_head * block_size + o) * X;
+  CT* vdst = value_cache + b * blk_elems + (int64_t)h0 * head_size * block_size + o;
+  const CT* ksrc = ks + j * rsk;
+  const CT* vsrc = vs + j * rsv;
+  const int n_groups = n / X;
+  const int64_t kstep = (int64_t)block_size * X;
+#pragma unroll 4
+  for (int u = r0; u < n_groups; u += RL)
+    *reinterpret_cast<int4*>(kdst + u * kstep) = *reinterpret_cast<const int4*>(ksrc + u * X);
+#pragma unroll 8
+  for (int e = r0; e < n; e += RL) vdst[(int64_t)e * block_size] = vsrc[e];
+}
+
 template <typename T, int KV>
 static int launch_reshape(const b200pa_reshape_params_t* p, cudaStream_t stream) {
   using CT = typename CacheStore<T, KV>::type;
@@ -122,6 +218,28 @@ static int launch_reshape(const b200pa_reshape_params_t* p, cudaStream_t stream)
                       (reinterpret_cast<uintptr_t>(p->key_cache) % 16 == 0) &&
                       (p->key_stride * sizeof(T)) % 16 == 0 && (p->value_stride * sizeof(T)) % 16 == 0;
   dim3 grid(p->num_tokens);
+  if (vec_ok && p->num_tokens >= kTileMinTokens && p->head_size % (16 / (int)sizeof(T)) == 0) {
+    const int n_max = 2048 / (int)sizeof(CT);  // elements of one token staged per CTA (K and V each)
+    if (p->head_size <= n_max) {
+      const int hpc = std::min(p->num_heads, std::max(1, n_max / p->head_size));
+      const size_t smem = (size_t)kTileTokens * ((size_t)hpc * p->head_size * 2 + X + 4 / sizeof(CT)) * sizeof(CT);
+      auto kernel = reshape_and_cache_tile_kernel<T, KV>;
+      static int configured[64] = {0};
+      int dev = 0;
+      B200PA_CUDA_CHECK(cudaGetDevice(&dev));
+      if (dev < 0 || dev >= 64 || configured[dev] < (int)smem) {
+        B200PA_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (dev >= 0 && dev < 64) configured[dev] = (int)smem;
+      }
+      dim3 tgrid((p->num_tokens + kTileTokens - 1) / kTileTokens, (p->num_heads + hpc - 1) / hpc);
+      kernel<<<tgrid, kTileThreads, smem, stream>>>(
+          static_cast<const T*>(p->key), static_cast<const T*>(p->value), static_cast<CT*>(p->key_cache),
+          static_cast<CT*>(p->value_cache), p->slot_mapping, p->key_stride, p->value_stride, p->num_tokens,
+          p->num_heads, p->head_size, p->block_size, hpc, p->kv_scale);
+      B200PA_CUDA_CHECK(cudaGetLastError());
+      return B200PA_OK;
+    }
+  }
   if (vec_ok) {
     int threads = std::min(std::max(n / X, 32), 256);
     threads = (threads + 31) / 32 * 32;
