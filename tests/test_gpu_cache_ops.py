@@ -190,13 +190,14 @@ def test_copy_blocks_many_layers_and_vs_reference_cuda(ops, ref_cuda):
 
 # ---------------------------------------------------------------------------------------- swap_blocks
 @pytest.mark.parametrize("direction", [("cuda", "cpu"), ("cuda", "cuda"), ("cpu", "cuda")])
+@pytest.mark.parametrize("pinned", [True, False])  # pinned host memory -> gather kernel, pageable -> memcpy runs
 @pytest.mark.parametrize("num_mappings", [256])
 @pytest.mark.parametrize("head_size", [64, 128])
 @pytest.mark.parametrize("block_size", [8, 16, 32])
 @pytest.mark.parametrize("dtype", [torch.half, torch.float])
 @pytest.mark.parametrize("kv_cache_dtype", ["auto", "fp8"])
 @torch.inference_mode()
-def test_swap_blocks(ops, oracle, direction, num_mappings, head_size, block_size, dtype, kv_cache_dtype):
+def test_swap_blocks(ops, oracle, direction, pinned, num_mappings, head_size, block_size, dtype, kv_cache_dtype):
     """tests/kernels/test_cache.py:274-344 — mapping on CPU, all three directions, exact."""
     random.seed(0)
     torch.manual_seed(0)
@@ -215,6 +216,11 @@ def test_swap_blocks(ops, oracle, direction, num_mappings, head_size, block_size
     conv = ops.convert_fp8 if dst_dev == "cuda" else oracle.convert_fp8
     dst_k, dst_v = helpers.create_kv_caches_with_random(num_blocks, block_size, 1, num_heads, head_size,
                                                         kv_cache_dtype, dtype, 1, dst_dev, conv)
+    if pinned:
+        if src_dev == "cpu":
+            src_k, src_v = [src_k[0].pin_memory()], [src_v[0].pin_memory()]
+        if dst_dev == "cpu":
+            dst_k, dst_v = [dst_k[0].pin_memory()], [dst_v[0].pin_memory()]
     src_k_clone, src_v_clone = src_k[0].clone(), src_v[0].clone()
     dst_k_before = dst_k[0].clone()
     ops.swap_blocks(src_k[0], dst_k[0], block_mapping)

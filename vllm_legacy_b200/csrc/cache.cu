@@ -9,6 +9,7 @@
 // but not their structure: 128-bit accesses where the layout allows, pointer tables passed as
 // kernel parameters (no per-call H2D copy / sync), swap runs merged into large async copies.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -319,6 +320,52 @@ __global__ void copy_blocks_byte_kernel(const __grid_constant__ LayerPtrs ptrs,
 }
 
 // =============================================================================================
+// swap_blocks: gather/scatter kernel over device-visible memory (HBM or mapped pinned host memory)
+// =============================================================================================
+
+constexpr int kSwapPairsPerLaunch = 1024;  // 16 KiB of kernel parameters (large-parameter launches, CUDA >= 12.1)
+
+struct SwapPairs {
+  int64_t src[kSwapPairsPerLaunch];
+  int64_t dst[kSwapPairsPerLaunch];
+};
+
+// grid (pairs, slices): every CTA copies one slice of one block with 128-bit accesses, 4 in flight per
+// thread.  Over PCIe this keeps thousands of reads/writes outstanding in ONE launch instead of one
+// cudaMemcpyAsync (~4 us of driver time each) per 32 KiB block.
+__global__ void __launch_bounds__(256)
+    swap_blocks_kernel(const __grid_constant__ SwapPairs pairs, const char* __restrict__ src, char* __restrict__ dst,
+                       int64_t vecs_per_block, int64_t vecs_per_slice) {
+  const int64_t s = pairs.src[blockIdx.x], d = pairs.dst[blockIdx.x];
+  const int4* sp = reinterpret_cast<const int4*>(src) + s * vecs_per_block;
+  int4* dp = reinterpret_cast<int4*>(dst) + d * vecs_per_block;
+  const int64_t begin = blockIdx.y * vecs_per_slice;
+  const int64_t end = min(begin + vecs_per_slice, vecs_per_block);
+  int64_t i = begin + threadIdx.x;
+  for (; i + 3 * 256 < end; i += 4 * 256) {
+    const int4 a = sp[i], b = sp[i + 256], c = sp[i + 512], e = sp[i + 768];
+    dp[i] = a;
+    dp[i + 256] = b;
+    dp[i + 512] = c;
+    dp[i + 768] = e;
+  }
+  for (; i < end; i += 256) dp[i] = sp[i];
+}
+
+// Device-visible alias of a pointer: device memory as is; pinned (page-locked, mapped) host memory through
+// its device pointer; pageable host memory -> nullptr (caller falls back to cudaMemcpyAsync).
+static const void* device_visible(const void* p) {
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return nullptr;
+  }
+  if (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged) return attr.devicePointer;
+  if (attr.type == cudaMemoryTypeHost) return attr.devicePointer;  // null when not mapped
+  return nullptr;
+}
+
+// =============================================================================================
 // convert_fp8
 // =============================================================================================
 
@@ -433,8 +480,33 @@ extern "C" int b200pa_swap_blocks(const void* src, void* dst, const int64_t* blo
   }
   const char* s = static_cast<const char*>(src);
   char* d = static_cast<char*>(dst);
-  // Merge runs (src+1 -> dst+1) into one copy: the scheduler hands out mostly-contiguous
-  // block ranges, and one large PCIe transfer beats many 32 KiB ones.
+  // Fast path: both sides visible to the device and 16-byte granular -> one gather kernel per 1024 pairs, the
+  // (host-resident) mapping travels as kernel parameters.  Destination blocks must be distinct (they are: the
+  // scheduler allocates them), as with any parallel copy.
+  static const bool no_kernel = std::getenv("B200PA_SWAP_MEMCPY") != nullptr;
+  if (!no_kernel && block_bytes % 16 == 0) {
+    const char* sv = static_cast<const char*>(device_visible(src));
+    char* dv = const_cast<char*>(static_cast<const char*>(device_visible(dst)));
+    if (sv && dv && reinterpret_cast<uintptr_t>(sv) % 16 == 0 && reinterpret_cast<uintptr_t>(dv) % 16 == 0) {
+      const int64_t vecs = block_bytes / 16;
+      // >= 2 slices per block keeps enough CTAs in flight for small mappings; 1024 vectors (16 KiB) per slice
+      const int64_t per_slice = std::max<int64_t>(256, std::min<int64_t>(1024, (vecs + 1) / 2));
+      const int slices = (int)((vecs + per_slice - 1) / per_slice);
+      for (int64_t p0 = 0; p0 < num_pairs; p0 += kSwapPairsPerLaunch) {
+        const int np = (int)std::min<int64_t>(kSwapPairsPerLaunch, num_pairs - p0);
+        SwapPairs pk;
+        for (int i = 0; i < np; ++i) {
+          pk.src[i] = block_mapping_host[2 * (p0 + i)];
+          pk.dst[i] = block_mapping_host[2 * (p0 + i) + 1];
+        }
+        swap_blocks_kernel<<<dim3(np, slices), 256, 0, stream>>>(pk, sv, dv, vecs, per_slice);
+        B200PA_CUDA_CHECK(cudaGetLastError());
+      }
+      return B200PA_OK;
+    }
+  }
+  // Fallback (pageable host memory / odd sizes): cudaMemcpyAsync per run of consecutive (src+1 -> dst+1)
+  // pairs — the scheduler hands out mostly-contiguous ranges, and one large transfer beats many small ones.
   int64_t i = 0;
   while (i < num_pairs) {
     const int64_t s0 = block_mapping_host[2 * i], d0 = block_mapping_host[2 * i + 1];
