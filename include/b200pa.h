@@ -141,6 +141,32 @@ typedef struct {
 int b200pa_reshape_and_cache(const b200pa_reshape_params_t* p, b200pa_stream_t stream);
 
 /*
+ * reshape_and_cache_flash  (flash-attention cache layout; "auto" KV dtype only, as the reference)
+ * replaces: csrc/cache.h:27-39, csrc/cache_kernels.cu:204-235 (kernel), :289-345 (host).
+ *   key, value   [num_tokens, num_heads, head_size] dtype, row strides key_stride/value_stride
+ *   key_cache    [num_blocks, block_size, num_heads, head_size], block stride block_stride (elements)
+ *   value_cache  same shape and block stride
+ *   slot_mapping [num_tokens] int64, slot < 0 = padding token (skipped)
+ */
+typedef struct {
+  const void* key;
+  const void* value;
+  void* key_cache;
+  void* value_cache;
+  const int64_t* slot_mapping;
+  int64_t key_stride;
+  int64_t value_stride;
+  int64_t block_stride;
+  int32_t num_tokens;
+  int32_t num_heads;
+  int32_t head_size;
+  int32_t block_size;
+  int32_t dtype; /* b200pa_dtype_t of key/value/cache */
+} b200pa_reshape_flash_params_t;
+
+int b200pa_reshape_and_cache_flash(const b200pa_reshape_flash_params_t* p, b200pa_stream_t stream);
+
+/*
  * copy_blocks
  * replaces: csrc/cache.h:11-13, csrc/cache_kernels.cu:68-146.
  *   key_cache_ptrs / value_cache_ptrs : HOST arrays of num_layers device pointers

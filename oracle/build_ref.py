@@ -7,7 +7,8 @@ into this repo), into oracle/_ref/ (git-ignored, NOT gpurun-ignored):
   ref_cpu_bf16.so / ref_cpu.so   csrc/cpu/attention.cpp + csrc/cpu/cache.cpp
                                  (AVX512 + OpenMP; with / without AVX512-BF16)
   ref_cuda.so                    csrc/attention/attention_kernels.cu +
-                                 csrc/cache_kernels.cu for sm_100a (≈15 min)
+                                 csrc/cache_kernels.cu + csrc/pos_encoding_kernels.cu
+                                 for sm_100a (≈15 min)
 
 Both are bound through the small pybind shims in this directory
 (ref_cpu_shim.cpp, ref_cuda_shim.cpp).  The reference's own build system
@@ -80,7 +81,8 @@ def build_cuda(force=False):
     inc, libdir, abi = _torch_flags()
     os.makedirs(os.path.join(OUT, "build"), exist_ok=True)
     cu = [os.path.join(CSRC, "attention", "attention_kernels.cu"),
-          os.path.join(CSRC, "cache_kernels.cu")]
+          os.path.join(CSRC, "cache_kernels.cu"),
+          os.path.join(CSRC, "pos_encoding_kernels.cu")]
     shim = os.path.join(HERE, "ref_cuda_shim.cpp")
     target = os.path.join(OUT, "ref_cuda.so")
     if not force and _fresh(target, cu + [shim]):
@@ -91,6 +93,9 @@ def build_cuda(force=False):
     for s in cu:
         o = os.path.join(OUT, "build", os.path.basename(s) + ".o")
         objs.append(o)
+        if not force and _fresh(o, [s]):  # the two big translation units take ~10 min each: reuse
+            print("up to date:", o)
+            continue
         cmd = ["nvcc", "-c", s, "-o", o, "-O2", "-std=c++17", "--threads", "4",
                "-gencode", "arch=compute_100a,code=sm_100a", "-DENABLE_FP8",
                "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-w",

@@ -122,6 +122,23 @@ def reshape_and_cache(key, value, key_cache, value_cache, slot_mapping, kv_cache
     assert rc == 0
 
 
+def reshape_and_cache_flash(key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype) -> None:
+    """csrc/cache_kernels.cu:204-235, 289-345; caches [nb, block_size, H, D] (only "auto")."""
+    if kv_cache_dtype != "auto":
+        raise RuntimeError(f"Unsupported data type of kv cache: {kv_cache_dtype}")
+    for t in (key, value, key_cache, value_cache, slot_mapping):
+        _cpu(t)
+    assert slot_mapping.dtype == torch.int64 and slot_mapping.is_contiguous()
+    assert key_cache.stride(0) == value_cache.stride(0) and key_cache[0].is_contiguous()
+    T, H, D = key.shape
+    rc = lib().oracle_reshape_and_cache_flash(
+        ctypes.c_void_p(key.data_ptr()), ctypes.c_void_p(value.data_ptr()), ctypes.c_void_p(key_cache.data_ptr()),
+        ctypes.c_void_p(value_cache.data_ptr()), ctypes.c_void_p(slot_mapping.data_ptr()), ctypes.c_int64(T),
+        ctypes.c_int64(key.stride(0)), ctypes.c_int64(value.stride(0)), ctypes.c_int64(key_cache.stride(0)),
+        ctypes.c_int(H), ctypes.c_int(D), ctypes.c_int(key_cache.shape[1]), ctypes.c_int(DT[key.dtype]))
+    assert rc == 0
+
+
 def copy_blocks(key_caches: List[torch.Tensor], value_caches: List[torch.Tensor], block_mapping) -> None:
     n = len(key_caches)
     if n == 0:

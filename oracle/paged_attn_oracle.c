@@ -206,6 +206,28 @@ int oracle_reshape_and_cache(const void* key, const void* value, void* key_cache
   return 0;
 }
 
+/* reshape_and_cache_flash — csrc/cache_kernels.cu:204-235: cache [nb, block_size, H, D] with block stride
+ * `block_stride` elements; tgt = block_idx*block_stride + block_offset*H*D + head_idx*D + head_offset (:226-230) */
+int oracle_reshape_and_cache_flash(const void* key, const void* value, void* k_cache, void* v_cache,
+                                   const int64_t* slot_mapping, int64_t num_tokens, int64_t key_stride,
+                                   int64_t value_stride, int64_t block_stride, int num_heads, int head_size,
+                                   int block_size, int dt) {
+  const int64_t n = (int64_t)num_heads * head_size;
+  const int es = elem_size(dt);
+  for (int64_t t = 0; t < num_tokens; ++t) {
+    const int64_t slot = slot_mapping[t];
+    if (slot < 0) continue; /* :218-221 */
+    const int64_t b = slot / block_size, o = slot % block_size;
+    for (int64_t i = 0; i < n; ++i) {
+      const int64_t h = i / head_size, d = i % head_size;
+      const int64_t tgt = b * block_stride + o * num_heads * head_size + h * head_size + d;
+      memcpy((char*)k_cache + tgt * es, (const char*)key + (t * key_stride + i) * es, es);
+      memcpy((char*)v_cache + tgt * es, (const char*)value + (t * value_stride + i) * es, es);
+    }
+  }
+  return 0;
+}
+
 /* copy_blocks — csrc/cache_kernels.cu:68-95: K_l[dst] = K_l[src], V_l[dst] = V_l[src] for every layer */
 int oracle_copy_blocks(void* const* key_caches, void* const* value_caches, int num_layers,
                        const int64_t* block_mapping, int64_t num_pairs, int64_t block_bytes) {

@@ -45,6 +45,13 @@ def ref_cuda():
 
 
 @pytest.fixture(scope="session")
+def ref_cuda_optional():
+    """ref_cuda when built, else None (for tests whose main checker is the CPU oracle)."""
+    from tests import helpers
+    return helpers.load_ref_cuda()
+
+
+@pytest.fixture(scope="session")
 def ops():
     """The product ops (CUDA extension).  Import fails loudly when the extension is missing."""
     from vllm_legacy_b200 import _custom_ops

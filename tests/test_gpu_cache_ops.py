@@ -344,3 +344,77 @@ def test_copy_blocks_golden_through_c_abi(golden):
 def test_get_max_shared_memory(ops):
     v = ops.get_max_shared_memory_per_block_device_attribute(0)
     assert v >= 200 * 1024  # B200: 227 KiB opt-in
+
+
+# -------------------------------------------------------------------------- reshape_and_cache_flash
+@pytest.mark.parametrize("num_tokens", [42])
+@pytest.mark.parametrize("num_heads", [8])
+@pytest.mark.parametrize("head_size", [64, 80, 96, 112, 128, 192, 256])
+@pytest.mark.parametrize("block_size", [8, 16, 32])
+@pytest.mark.parametrize("dtype", DTYPES)
+@torch.inference_mode()
+def test_reshape_and_cache_flash(ops, oracle, num_tokens, num_heads, head_size, block_size, dtype):
+    """tests/kernels/test_cache.py:196-282 — flash layout [nb, B, H, D], strided K/V rows, random unique slots,
+    plus a padding slot.  Bit-exact vs the oracle and vs the test's own index assignment."""
+    random.seed(0)
+    torch.manual_seed(0)
+    num_blocks = 64
+    slot_mapping = torch.tensor(random.sample(range(num_blocks * block_size), num_tokens), dtype=torch.long)
+    slot_mapping[5] = -1
+    qkv = torch.randn(num_tokens, 3, num_heads, head_size, dtype=dtype)
+    _, key, value = qkv.unbind(dim=1)
+    scale = head_size ** -0.5
+    kc_ref = torch.empty(num_blocks, block_size, num_heads, head_size, dtype=dtype).uniform_(-scale, scale)
+    vc_ref = torch.empty_like(kc_ref).uniform_(-scale, scale)
+    kc, vc = kc_ref.to(DEV), vc_ref.to(DEV)
+    _, key_d, value_d = qkv.to(DEV).unbind(dim=1)
+    ops.reshape_and_cache_flash(key_d, value_d, kc, vc, slot_mapping.to(DEV), "auto")
+    expect_k, expect_v = kc_ref.clone(), vc_ref.clone()
+    oracle.reshape_and_cache_flash(key, value, kc_ref, vc_ref, slot_mapping, "auto")
+    for i, s in enumerate(slot_mapping.tolist()):
+        if s >= 0:
+            expect_k[s // block_size, s % block_size] = key[i]
+            expect_v[s // block_size, s % block_size] = value[i]
+    assert torch.equal(_bits(kc_ref), _bits(expect_k)) and torch.equal(_bits(vc_ref), _bits(expect_v))
+    assert torch.equal(_bits(kc.cpu()), _bits(kc_ref))
+    assert torch.equal(_bits(vc.cpu()), _bits(vc_ref))
+
+
+@torch.inference_mode()
+def test_reshape_and_cache_flash_variants(ops, oracle, ref_cuda_optional):
+    """Large prefill-sized call (grid-stride path), a block-strided cache view (block_stride > B*H*D), a
+    misaligned source (scalar kernel), empty input and the fp8 rejection (cache_kernels.cu:303-306)."""
+    torch.manual_seed(0)
+    T, H, D, B, NB = 5000, 8, 128, 16, 400
+    dtype = torch.bfloat16
+    slots = torch.randperm(NB * B)[:T]
+    key = torch.randn(T, H, D, dtype=dtype)
+    value = torch.randn(T, H, D, dtype=dtype)
+    big = torch.zeros(NB, 2, B, H, D, dtype=dtype)      # K and V interleaved per block: stride(0) = 2*B*H*D
+    kc_ref, vc_ref = big[:, 0], big[:, 1]
+    big_d = big.to(DEV)
+    kc, vc = big_d[:, 0], big_d[:, 1]
+    ops.reshape_and_cache_flash(key.to(DEV), value.to(DEV), kc, vc, slots.to(DEV), "auto")
+    oracle.reshape_and_cache_flash(key, value, kc_ref, vc_ref, slots, "auto")
+    assert torch.equal(_bits(big_d.cpu()), _bits(big))
+    if ref_cuda_optional is not None:
+        big2 = torch.zeros_like(big_d)
+        ref_cuda_optional.reshape_and_cache_flash(key.to(DEV), value.to(DEV), str(big2[:, 0].data_ptr()), B,
+                                                  big2.stride(0), str(big2[:, 1].data_ptr()), big2.stride(0),
+                                                  slots.to(DEV), "auto")
+        assert torch.equal(_bits(big2), _bits(big_d))
+    # misaligned rows -> scalar kernel
+    flat = torch.randn(2 * 7 * 3 * 64 + 8, dtype=dtype)
+    k2, v2 = flat[1:1 + 7 * 192].view(7, 3, 64), flat[7 * 192 + 3:2 * 7 * 192 + 3].view(7, 3, 64)
+    flat_d = flat.to(DEV)
+    k2d, v2d = flat_d[1:1 + 7 * 192].view(7, 3, 64), flat_d[7 * 192 + 3:2 * 7 * 192 + 3].view(7, 3, 64)
+    c_ref = torch.zeros(2, 4, 16, 3, 64, dtype=dtype)
+    c_d = c_ref.to(DEV)
+    s2 = torch.tensor([5, 0, 63, 17, -1, 31, 32], dtype=torch.long)
+    ops.reshape_and_cache_flash(k2d, v2d, c_d[0], c_d[1], s2.to(DEV), "auto")
+    oracle.reshape_and_cache_flash(k2, v2, c_ref[0], c_ref[1], s2, "auto")
+    assert torch.equal(_bits(c_d.cpu()), _bits(c_ref))
+    ops.reshape_and_cache_flash(k2d[:0], v2d[:0], c_d[0], c_d[1], s2[:0].to(DEV), "auto")
+    assert torch.equal(_bits(c_d.cpu()), _bits(c_ref))
+    with pytest.raises(RuntimeError, match="Unsupported data type of kv cache"):
+        ops.reshape_and_cache_flash(k2d, v2d, c_d[0], c_d[1], s2.to(DEV), "fp8")

@@ -259,3 +259,27 @@ def test_attention_blocksparse_masks_blocks(oracle):
             w = torch.softmax((scale * keys[:, kvh] @ q[0, h]).masked_fill(~mask, float("-inf")), 0)
             want = w @ vals[:, kvh]
             assert torch.allclose(out[0, h], want, atol=1e-5, rtol=1e-4), (slide, h)
+
+
+@pytest.mark.parametrize("dtype", [torch.half, torch.bfloat16, torch.float])
+@pytest.mark.parametrize("block_size", [8, 16, 32])
+def test_oracle_reshape_and_cache_flash_matches_reference_test_loop(oracle, dtype, block_size):
+    """oracle.reshape_and_cache_flash == the index assignment of tests/kernels/test_cache.py:265-279."""
+    torch.manual_seed(0)
+    T, H, D, NB = 42, 8, 80, 32
+    slots = torch.randperm(NB * block_size)[:T]
+    slots[7] = -1
+    qkv = torch.randn(T, 3, H, D, dtype=dtype)
+    _, key, value = qkv.unbind(dim=1)
+    kc = torch.randn(NB, block_size, H, D, dtype=dtype)
+    vc = torch.randn(NB, block_size, H, D, dtype=dtype)
+    ek, ev = kc.clone(), vc.clone()
+    oracle.reshape_and_cache_flash(key, value, kc, vc, slots, "auto")
+    for i, s in enumerate(slots.tolist()):
+        if s >= 0:
+            ek[s // block_size, s % block_size] = key[i]
+            ev[s // block_size, s % block_size] = value[i]
+    assert torch.equal(kc.view(torch.uint8), ek.view(torch.uint8))
+    assert torch.equal(vc.view(torch.uint8), ev.view(torch.uint8))
+    with pytest.raises(RuntimeError, match="Unsupported data type of kv cache"):
+        oracle.reshape_and_cache_flash(key, value, kc, vc, slots, "fp8")

@@ -96,6 +96,24 @@ def reshape_and_cache(
         slot_mapping, kv_cache_dtype, kv_scale)
 
 
+def reshape_and_cache_flash(
+    key: torch.Tensor,
+    value: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    slot_mapping: torch.Tensor,
+    kv_cache_dtype: str,
+) -> None:
+    # Same tensor-taking signature as vllm/_custom_ops.py:326-335; the fork's wrapper forwards the tensors
+    # to a pybind function that expects pointer strings (csrc/cache.h:27-39) and cannot work as shipped —
+    # here the marshalling matches the C++ side (as vllm/attention/backends/flash_attn.py:288-298 does by hand).
+    vllm_cache_ops.reshape_and_cache_flash(
+        key, value,
+        str(key_cache.data_ptr()), key_cache.size(1), key_cache.stride(0),
+        str(value_cache.data_ptr()), value_cache.stride(0),
+        slot_mapping, kv_cache_dtype)
+
+
 def copy_blocks(key_caches: List[torch.Tensor], value_caches: List[torch.Tensor],
                 block_mapping: torch.Tensor) -> None:
     vllm_cache_ops.copy_blocks(key_caches, value_caches, block_mapping)

@@ -185,6 +185,39 @@ void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, const std::stri
   check_status(b200pa_reshape_and_cache(&p, current_stream()), nullptr, key, kv_cache_dtype);
 }
 
+// csrc/cache.h:27-39 (fork ABI: cache pointers as decimal strings + block size / block strides)
+void reshape_and_cache_flash(torch::Tensor& key, torch::Tensor& value, const std::string& key_cache_data_ptr_str,
+                             int key_cache_size_1, int key_cache_stride_0, const std::string& value_cache_data_ptr_str,
+                             int value_cache_stride_0, torch::Tensor& slot_mapping, const std::string& kv_cache_dtype) {
+  // cache_kernels.cu:303-306: only the "auto" KV dtype
+  if (kv_cache_dtype != "auto") TORCH_CHECK(false, "Unsupported data type of kv cache: ", kv_cache_dtype);
+  TORCH_CHECK(key.is_cuda() && value.is_cuda() && slot_mapping.is_cuda(),
+              "b200pa reshape_and_cache_flash: tensors must be on a CUDA device (there is no CPU path)");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long && slot_mapping.is_contiguous(),
+              "slot_mapping must be contiguous int64");
+  TORCH_CHECK(key.dim() == 3 && key.stride(2) == 1 && key.stride(1) == key.size(2) && value.stride(2) == 1 &&
+                  value.stride(1) == value.size(2),
+              "key/value must be [num_tokens, num_heads, head_size] with contiguous heads");
+  TORCH_CHECK(key_cache_stride_0 == value_cache_stride_0, "k_cache and v_cache must have the same block stride");
+  b200pa_reshape_flash_params_t p{};
+  p.key = key.data_ptr();
+  p.value = value.data_ptr();
+  p.key_cache = parse_ptr(key_cache_data_ptr_str);
+  p.value_cache = parse_ptr(value_cache_data_ptr_str);
+  p.slot_mapping = slot_mapping.data_ptr<int64_t>();
+  p.key_stride = key.stride(0);
+  p.value_stride = value.stride(0);
+  p.block_stride = key_cache_stride_0;
+  p.num_tokens = key.size(0);
+  p.num_heads = key.size(1);
+  p.head_size = key.size(2);
+  p.block_size = key_cache_size_1;
+  p.dtype = scalar_dtype(key);
+  if (p.dtype < 0 || p.dtype == B200PA_U8) TORCH_CHECK(false, "Unsupported input type of kv cache: ", key.scalar_type());
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(key));
+  check_status(b200pa_reshape_and_cache_flash(&p, current_stream()), nullptr, key, kv_cache_dtype);
+}
+
 // csrc/cache.h:11-13
 void copy_blocks(std::vector<torch::Tensor>& key_caches, std::vector<torch::Tensor>& value_caches,
                  const torch::Tensor& block_mapping) {
@@ -277,6 +310,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   cache_ops.def("swap_blocks", &swap_blocks, "Swap in (out) the cache blocks from src to dst");
   cache_ops.def("copy_blocks", &copy_blocks, "Copy the cache blocks from src to dst");
   cache_ops.def("reshape_and_cache", &reshape_and_cache, "Reshape the key and value tensors and cache them");
+  cache_ops.def("reshape_and_cache_flash", &reshape_and_cache_flash,
+                "Reshape the key and value tensors and cache them (flash-attention layout)");
   cache_ops.def("convert_fp8", &convert_fp8, "Convert the key and value cache to fp8 data type");
   // csrc/pybind.cpp:87-95
   pybind11::module cuda_utils = m.def_submodule("cuda_utils", "vLLM cuda utils (B200)");
