@@ -167,6 +167,54 @@ typedef struct {
 int b200pa_reshape_and_cache_flash(const b200pa_reshape_flash_params_t* p, b200pa_stream_t stream);
 
 /*
+ * rotary_embedding / batched_rotary_embedding, optionally FUSED with reshape_and_cache
+ * replaces: csrc/ops.h:38-47, csrc/pos_encoding_kernels.cu:10-201 (GPT-NeoX and GPT-J styles,
+ *           in place on query and key) and, when key_cache != NULL, additionally the
+ *           reshape_and_cache call that follows it in the decode step
+ *           (vllm/model_executor/models/llama.py:164-171 -> vllm/attention/ops/paged_attn.py:62-79,
+ *           csrc/cache_kernels.cu:150-202): the rotated key and the value of every token with
+ *           slot >= 0 are written to the paged cache by the same launch.  Results are bit-identical
+ *           to the two reference launches run back to back.
+ *   positions             : [num_tokens] int64
+ *   query / key           : [num_tokens, num_heads|num_kv_heads, head_size], token stride in elements
+ *   cos_sin_cache         : [max_position, rot_dim] (cos half, sin half), same dtype as query
+ *   cos_sin_cache_offsets : NULL (rotary_embedding) or [num_tokens] int64 (batched variant)
+ *   value/key_cache/value_cache/slot_mapping/block_size/x/kv_dtype/kv_scale : as reshape_and_cache;
+ *                           key_cache == NULL selects the plain rotary op.
+ * Arithmetic follows the reference exactly: every product and sum is rounded to the tensor dtype
+ * (c10::Half / c10::BFloat16 operators), fp32 uses fma(x, cos, -(y*sin)) / fma(y, cos, x*sin) as
+ * nvcc contracts the reference expression.
+ */
+typedef struct {
+  const int64_t* positions;
+  void* query;
+  void* key;
+  const void* cos_sin_cache;
+  const int64_t* cos_sin_cache_offsets;
+  int64_t query_stride;
+  int64_t key_stride;
+  int32_t num_tokens;
+  int32_t num_heads;
+  int32_t num_kv_heads;
+  int32_t head_size;
+  int32_t rot_dim;
+  int32_t is_neox;
+  int32_t dtype; /* b200pa_dtype_t of query/key/value/cos_sin_cache */
+  /* fused cache write (all NULL / 0 for the plain op) */
+  const void* value;
+  int64_t value_stride;
+  void* key_cache;
+  void* value_cache;
+  const int64_t* slot_mapping;
+  int32_t block_size;
+  int32_t x;
+  int32_t kv_dtype; /* b200pa_kv_dtype_t */
+  float kv_scale;
+} b200pa_rope_params_t;
+
+int b200pa_rotary_embedding(const b200pa_rope_params_t* p, b200pa_stream_t stream);
+
+/*
  * copy_blocks
  * replaces: csrc/cache.h:11-13, csrc/cache_kernels.cu:68-146.
  *   key_cache_ptrs / value_cache_ptrs : HOST arrays of num_layers device pointers

@@ -139,6 +139,34 @@ def reshape_and_cache_flash(key, value, key_cache, value_cache, slot_mapping, kv
     assert rc == 0
 
 
+def rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox, rot_dim=None,
+                     cos_sin_cache_offsets=None) -> None:
+    """csrc/pos_encoding_kernels.cu:10-201, in place on query and key; with cos_sin_cache_offsets it is the
+    batched form (:95-131, :166-201)."""
+    for t in (positions, query, key, cos_sin_cache):
+        _cpu(t)
+    assert positions.dtype == torch.int64 and positions.is_contiguous() and cos_sin_cache.is_contiguous()
+    assert query.stride(-1) == 1 and key.stride(-1) == 1 and query.dtype == key.dtype == cos_sin_cache.dtype
+    if rot_dim is None:
+        rot_dim = cos_sin_cache.shape[1]
+    if cos_sin_cache_offsets is not None:
+        _cpu(cos_sin_cache_offsets)
+        assert cos_sin_cache_offsets.dtype == torch.int64 and cos_sin_cache_offsets.is_contiguous()
+        num_tokens = cos_sin_cache_offsets.shape[0]
+        off = ctypes.c_void_p(cos_sin_cache_offsets.data_ptr())
+    else:
+        num_tokens = query.numel() // query.shape[-1]
+        off = ctypes.c_void_p(None)
+    rc = lib().oracle_rotary_embedding(
+        ctypes.c_void_p(positions.data_ptr()), ctypes.c_void_p(query.data_ptr()), ctypes.c_void_p(key.data_ptr()),
+        ctypes.c_void_p(cos_sin_cache.data_ptr()), off, ctypes.c_int64(num_tokens),
+        ctypes.c_int64(query.stride(-2)), ctypes.c_int64(key.stride(-2)),
+        ctypes.c_int(query.shape[-1] // head_size), ctypes.c_int(key.shape[-1] // head_size),
+        ctypes.c_int(head_size), ctypes.c_int(rot_dim), ctypes.c_int(1 if is_neox else 0),
+        ctypes.c_int(DT[query.dtype]))
+    assert rc == 0
+
+
 def copy_blocks(key_caches: List[torch.Tensor], value_caches: List[torch.Tensor], block_mapping) -> None:
     n = len(key_caches)
     if n == 0:

@@ -228,6 +228,55 @@ int oracle_reshape_and_cache_flash(const void* key, const void* value, void* k_c
   return 0;
 }
 
+/* ---------------------------------------------------------------------------------------------
+ * rotary_embedding / batched_rotary_embedding — csrc/pos_encoding_kernels.cu:10-131.
+ * apply_token_rotary_embedding (:10-36): NeoX pairs (i, embed+i) with cos[i], sin[i]; GPT-J pairs
+ * (2i, 2i+1) with cos[i], sin[i]; arr[x] = x*cos - y*sin; arr[y] = y*cos + x*sin evaluated with
+ * scalar_t operators: for c10::Half / c10::BFloat16 every product and sum is computed in fp32 and
+ * rounded back to the 16-bit type (torch/headeronly/util/Half.h:501-511, BFloat16.h:185-198); for
+ * float nvcc contracts to fma(x, cos, -(y*sin)) and fma(y, cos, x*sin) (SASS of the reference
+ * build: FMUL, FMUL, FFMA, FFMA).  offsets == NULL: rotary_embedding (:70-93), else the batched
+ * form (:95-131) with cache row pos + offset.
+ * --------------------------------------------------------------------------------------------- */
+static void rotate_pair(void* arr, int64_t xi, int64_t yi, float c, float s, int dt) {
+  const float x = load_elem(arr, xi, dt), y = load_elem(arr, yi, dt);
+  float nx, ny;
+  if (dt == DT_F32) {
+    nx = fmaf(x, c, -(y * s));
+    ny = fmaf(y, c, x * s);
+  } else {
+    nx = round_to(x * c, dt) - round_to(y * s, dt);
+    ny = round_to(y * c, dt) + round_to(x * s, dt);
+  }
+  store_elem(arr, xi, dt, nx);
+  store_elem(arr, yi, dt, ny);
+}
+
+int oracle_rotary_embedding(const int64_t* positions, void* query, void* key, const void* cos_sin_cache,
+                            const int64_t* offsets, int64_t num_tokens, int64_t query_stride, int64_t key_stride,
+                            int num_heads, int num_kv_heads, int head_size, int rot_dim, int is_neox, int dt) {
+  const int embed = rot_dim / 2;
+  for (int64_t t = 0; t < num_tokens; ++t) {
+    const int64_t pos = positions[t] + (offsets ? offsets[t] : 0);
+    const int64_t cbase = pos * rot_dim;
+    for (int pass = 0; pass < 2; ++pass) {
+      void* base = pass == 0 ? query : key;
+      const int nh = pass == 0 ? num_heads : num_kv_heads;
+      const int64_t stride = pass == 0 ? query_stride : key_stride;
+      for (int h = 0; h < nh; ++h) {
+        const int64_t th = t * stride + (int64_t)h * head_size;
+        for (int i = 0; i < embed; ++i) {
+          const float c = load_elem(cos_sin_cache, cbase + i, dt);
+          const float s = load_elem(cos_sin_cache, cbase + embed + i, dt);
+          if (is_neox) rotate_pair(base, th + i, th + embed + i, c, s, dt);
+          else rotate_pair(base, th + 2 * i, th + 2 * i + 1, c, s, dt);
+        }
+      }
+    }
+  }
+  return 0;
+}
+
 /* copy_blocks — csrc/cache_kernels.cu:68-95: K_l[dst] = K_l[src], V_l[dst] = V_l[src] for every layer */
 int oracle_copy_blocks(void* const* key_caches, void* const* value_caches, int num_layers,
                        const int64_t* block_mapping, int64_t num_pairs, int64_t block_bytes) {

@@ -283,3 +283,44 @@ def test_oracle_reshape_and_cache_flash_matches_reference_test_loop(oracle, dtyp
     assert torch.equal(vc.view(torch.uint8), ev.view(torch.uint8))
     with pytest.raises(RuntimeError, match="Unsupported data type of kv cache"):
         oracle.reshape_and_cache_flash(key, value, kc, vc, slots, "fp8")
+
+
+# ------------------------------------------------------------------------------------- rotary_embedding
+def _rope_native(positions, query, key, head_size, cache, is_neox):
+    """vllm/model_executor/layers/rotary_embedding.py:105-147 (_forward_native), the checker the reference's
+    own tests/kernels/test_pos_encoding.py uses; evaluated per-op in the tensor dtype like the CUDA kernel."""
+    rot = cache.shape[1]
+    cos, sin = cache[positions.flatten()].chunk(2, dim=-1)
+    cos, sin = cos[:, None, :], sin[:, None, :]
+    outs = []
+    for a in (query, key):
+        a = a.reshape(positions.numel(), -1, head_size).clone()
+        x, y = (a[..., :rot // 2], a[..., rot // 2:rot]) if is_neox else (a[..., 0:rot:2], a[..., 1:rot:2])
+        nx, ny = x * cos - y * sin, y * cos + x * sin
+        if is_neox:
+            a[..., :rot // 2], a[..., rot // 2:rot] = nx, ny
+        else:
+            a[..., 0:rot:2], a[..., 1:rot:2] = nx, ny
+        outs.append(a)
+    return outs
+
+
+@pytest.mark.parametrize("is_neox", [True, False])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("head_size,rot", [(64, 64), (80, 32), (128, 128), (256, 32)])
+def test_oracle_rotary_embedding_vs_native(oracle, is_neox, dtype, head_size, rot):
+    torch.manual_seed(0)
+    T, H, Hkv = 23, 7, 3
+    inv = 1.0 / (10000 ** (torch.arange(0, rot, 2, dtype=torch.float) / rot))
+    fr = torch.einsum("i,j -> ij", torch.arange(512, dtype=torch.float), inv)
+    cache = torch.cat((fr.cos(), fr.sin()), dim=-1).to(dtype)
+    positions = torch.randint(0, 512, (T,))
+    q = torch.randn(T, H * head_size, dtype=dtype)
+    k = torch.randn(T, Hkv * head_size, dtype=dtype)
+    want_q, want_k = _rope_native(positions, q, k, head_size, cache, is_neox)
+    oracle.rotary_embedding(positions, q, k, head_size, cache, is_neox)
+    if dtype == torch.float32:  # the kernel's fma contraction differs from torch's separate ops by <= 1 ulp
+        torch.testing.assert_close(q.view(T, H, head_size), want_q, atol=1e-6, rtol=1e-6)
+        torch.testing.assert_close(k.view(T, Hkv, head_size), want_k, atol=1e-6, rtol=1e-6)
+    else:
+        assert torch.equal(q.view(T, H, head_size), want_q) and torch.equal(k.view(T, Hkv, head_size), want_k)

@@ -79,6 +79,31 @@ def paged_attention_v2(
         blocksparse_block_size, blocksparse_head_sliding_step)
 
 
+# pos encoding ops (vllm/_custom_ops.py:103-124); in place on query and key
+def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor, head_size: int,
+                     cos_sin_cache: torch.Tensor, is_neox: bool) -> None:
+    vllm_ops.rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox)
+
+
+def batched_rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor, head_size: int,
+                             cos_sin_cache: torch.Tensor, is_neox: bool, rot_dim: int,
+                             cos_sin_cache_offsets: torch.Tensor) -> None:
+    vllm_ops.batched_rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox, rot_dim,
+                                      cos_sin_cache_offsets)
+
+
+def rotary_embedding_reshape_and_cache(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
+                                       value: torch.Tensor, head_size: int, cos_sin_cache: torch.Tensor,
+                                       is_neox: bool, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                                       slot_mapping: torch.Tensor, kv_cache_dtype: str, kv_scale: float) -> None:
+    """rotary_embedding(positions, query, key, ...) followed by reshape_and_cache(key, value, ...) in ONE launch
+    (SURVEY 8f rank 2); bit-identical to the two reference calls.  Not in the reference."""
+    vllm_ops.rotary_embedding_reshape_and_cache(
+        positions, query, key, value, head_size, cos_sin_cache, is_neox,
+        str(key_cache.data_ptr()), key_cache.size(3), key_cache.size(4), str(value_cache.data_ptr()),
+        slot_mapping, kv_cache_dtype, kv_scale)
+
+
 # cache ops
 def reshape_and_cache(
     key: torch.Tensor,

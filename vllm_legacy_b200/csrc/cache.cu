@@ -24,17 +24,6 @@ thread_local int g_last_attention_partitions = 0;
 // reshape_and_cache
 // =============================================================================================
 
-template <typename T, int KV>
-struct CacheStore {
-  using type = uint8_t;
-  static __device__ __forceinline__ uint8_t cvt(T v, float scale) { return fp8_quant<KV, T>(v, scale); }
-};
-template <typename T>
-struct CacheStore<T, B200PA_KV_AUTO> {
-  using type = T;
-  static __device__ __forceinline__ T cvt(T v, float) { return v; }
-};
-
 // Generic path: any x, any alignment.  One CTA per token, one element per thread-iteration.
 // Index math as cache_kernels.cu:169-200.
 template <typename T, int KV>

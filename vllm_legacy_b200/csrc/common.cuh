@@ -89,6 +89,18 @@ struct CacheElem<T, B200PA_KV_AUTO> {
   static __device__ __forceinline__ float load(const T* p, float) { return to_float<T>(*p); }
 };
 
+// Store side: element written to the cache for a source element of type T (KV == AUTO: unchanged).
+template <typename T, int KV>
+struct CacheStore {
+  using type = uint8_t;
+  static __device__ __forceinline__ uint8_t cvt(T v, float scale) { return fp8_quant<KV, T>(v, scale); }
+};
+template <typename T>
+struct CacheStore<T, B200PA_KV_AUTO> {
+  using type = T;
+  static __device__ __forceinline__ T cvt(T v, float) { return v; }
+};
+
 // ---- 128-bit streaming accesses ----------------------------------------------------------------
 __device__ __forceinline__ int4 ld_nc_v4(const void* ptr) {
   int4 r;

@@ -218,6 +218,87 @@ void reshape_and_cache_flash(torch::Tensor& key, torch::Tensor& value, const std
   check_status(b200pa_reshape_and_cache_flash(&p, current_stream()), nullptr, key, kv_cache_dtype);
 }
 
+// csrc/ops.h:38-47 (rotary_embedding / batched_rotary_embedding) and the fused
+// rotary + reshape_and_cache decode-step op (not in the reference; bit-identical to the two calls).
+static void rope_common(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int head_size,
+                        torch::Tensor& cos_sin_cache, bool is_neox, int rot_dim, const int64_t* offsets,
+                        int64_t num_tokens, b200pa_rope_params_t& p) {
+  TORCH_CHECK(query.is_cuda() && key.is_cuda() && positions.is_cuda() && cos_sin_cache.is_cuda(),
+              "b200pa rotary_embedding: tensors must be on a CUDA device (there is no CPU path)");
+  TORCH_CHECK(positions.scalar_type() == at::ScalarType::Long && positions.is_contiguous(),
+              "positions must be contiguous int64");
+  TORCH_CHECK(cos_sin_cache.is_contiguous() && cos_sin_cache.scalar_type() == query.scalar_type() &&
+                  key.scalar_type() == query.scalar_type(),
+              "query, key and cos_sin_cache must share one dtype");
+  TORCH_CHECK(query.stride(-1) == 1 && key.stride(-1) == 1, "query/key must have a contiguous last dimension");
+  p.positions = positions.data_ptr<int64_t>();
+  p.query = query.data_ptr();
+  p.key = key.data_ptr();
+  p.cos_sin_cache = cos_sin_cache.data_ptr();
+  p.cos_sin_cache_offsets = offsets;
+  p.query_stride = query.stride(-2);
+  p.key_stride = key.stride(-2);
+  p.num_tokens = num_tokens;
+  p.num_heads = query.size(-1) / head_size;
+  p.num_kv_heads = key.size(-1) / head_size;
+  p.head_size = head_size;
+  p.rot_dim = rot_dim;
+  p.is_neox = is_neox ? 1 : 0;
+  p.dtype = scalar_dtype(query);
+  if (p.dtype < 0 || p.dtype == B200PA_U8) TORCH_CHECK(false, "rotary_embedding: unsupported dtype ", query.scalar_type());
+}
+
+void rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int head_size,
+                      torch::Tensor& cos_sin_cache, bool is_neox) {
+  b200pa_rope_params_t p{};
+  rope_common(positions, query, key, head_size, cos_sin_cache, is_neox, cos_sin_cache.size(1), nullptr,
+              query.numel() / query.size(-1), p);
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
+  check_status(b200pa_rotary_embedding(&p, current_stream()), nullptr, query, "auto");
+}
+
+void batched_rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int head_size,
+                              torch::Tensor& cos_sin_cache, bool is_neox, int rot_dim,
+                              torch::Tensor& cos_sin_cache_offsets) {
+  TORCH_CHECK(cos_sin_cache_offsets.is_cuda() && cos_sin_cache_offsets.scalar_type() == at::ScalarType::Long &&
+                  cos_sin_cache_offsets.is_contiguous(),
+              "cos_sin_cache_offsets must be a contiguous CUDA int64 tensor");
+  b200pa_rope_params_t p{};
+  rope_common(positions, query, key, head_size, cos_sin_cache, is_neox, rot_dim,
+              cos_sin_cache_offsets.data_ptr<int64_t>(), cos_sin_cache_offsets.size(0), p);
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
+  check_status(b200pa_rotary_embedding(&p, current_stream()), nullptr, query, "auto");
+}
+
+void rotary_embedding_reshape_and_cache(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key,
+                                        torch::Tensor& value, int head_size, torch::Tensor& cos_sin_cache,
+                                        bool is_neox, const std::string& key_cache_data_ptr_str,
+                                        int key_cache_block_size, int key_cache_x,
+                                        const std::string& value_cache_data_ptr_str, torch::Tensor& slot_mapping,
+                                        const std::string& kv_cache_dtype, float kv_scale) {
+  const int kv = parse_kv_dtype(kv_cache_dtype);
+  b200pa_rope_params_t p{};
+  rope_common(positions, query, key, head_size, cos_sin_cache, is_neox, cos_sin_cache.size(1), nullptr,
+              query.numel() / query.size(-1), p);
+  TORCH_CHECK(value.is_cuda() && slot_mapping.is_cuda() && value.scalar_type() == query.scalar_type() &&
+                  value.stride(-1) == 1,
+              "value must be a CUDA tensor of the query dtype with a contiguous last dimension");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long && slot_mapping.is_contiguous() &&
+                  slot_mapping.numel() == p.num_tokens,
+              "slot_mapping must be contiguous int64 [num_tokens]");
+  p.value = value.data_ptr();
+  p.value_stride = value.dim() == 3 ? value.stride(0) : value.stride(-2);
+  p.key_cache = parse_ptr(key_cache_data_ptr_str);
+  p.value_cache = parse_ptr(value_cache_data_ptr_str);
+  p.slot_mapping = slot_mapping.data_ptr<int64_t>();
+  p.block_size = key_cache_block_size;
+  p.x = key_cache_x;
+  p.kv_dtype = kv;
+  p.kv_scale = kv_scale;
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
+  check_status(b200pa_rotary_embedding(&p, current_stream()), nullptr, query, kv_cache_dtype);
+}
+
 // csrc/cache.h:11-13
 void copy_blocks(std::vector<torch::Tensor>& key_caches, std::vector<torch::Tensor>& value_caches,
                  const torch::Tensor& block_mapping) {
@@ -305,6 +386,12 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   ops.def("paged_attention_v1", &paged_attention_v1,
           "Compute the attention between an input query and the cached keys/values using PagedAttention.");
   ops.def("paged_attention_v2", &paged_attention_v2, "PagedAttention V2.");
+  // csrc/pybind.cpp:33-38
+  ops.def("rotary_embedding", &rotary_embedding, "Apply GPT-NeoX or GPT-J style rotary embedding to query and key");
+  ops.def("batched_rotary_embedding", &batched_rotary_embedding,
+          "Apply GPT-NeoX or GPT-J style rotary embedding to query and key (batched cos/sin offsets)");
+  ops.def("rotary_embedding_reshape_and_cache", &rotary_embedding_reshape_and_cache,
+          "rotary_embedding on query/key fused with reshape_and_cache of the rotated key and the value");
   // csrc/pybind.cpp:74-84
   pybind11::module cache_ops = m.def_submodule("cache_ops", "vLLM cache ops (B200)");
   cache_ops.def("swap_blocks", &swap_blocks, "Swap in (out) the cache blocks from src to dst");
