@@ -13,4 +13,4 @@ timeout 300 $CMD > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
 timeout 300 $CMD > gpurun_out/plain2.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:paged_attention_mma -s 5 -c 2 -o gpurun_out/prof_mma $CMD > gpurun_out/ncu_full.log 2>&1
-tail -3 gpurun_out/pytest_props.log gpurun_out/smoke.log gpurun_out/bench_ours.json gpurun_out/bench_ref.json
+tail -n 3 gpurun_out/pytest_props.log gpurun_out/smoke.log gpurun_out/bench_ours.json gpurun_out/bench_ref.json
