@@ -215,6 +215,62 @@ typedef struct {
 int b200pa_rotary_embedding(const b200pa_rope_params_t* p, b200pa_stream_t stream);
 
 /*
+ * context_attention_fwd (prefix-prefill / chunked-prefill attention over the paged cache)
+ * replaces: vllm/attention/ops/prefix_prefill.py:684-817 (host wrapper) and the Triton kernels
+ *           _fwd_kernel (:10-245) and _fwd_kernel_alibi (:442-681); called from
+ *           vllm/attention/ops/paged_attn.py:185-216 (PagedAttention.forward_prefix).
+ *
+ * For sequence b with ctx = ctx_lens[b] cached tokens and q_len = seq_lens[b] - ctx new tokens whose
+ * rows start at start_loc[b] in query/key/value/out, new token m attends to the cached keys 0..ctx-1
+ * (read through block_tables[b] from the paged cache) and to the new keys 0..m (causal):
+ *   out[m] = softmax_j(scale * q[m].k[j] + bias) . v[j]
+ * bias: ALiBi slope_h * (kpos - qpos) when alibi_slopes != NULL (the window is then ignored, as in the
+ * reference, :717-760); else keys with qpos - kpos >= sliding_window are masked when sliding_window > 0.
+ *
+ * Layouts:
+ *   query, out     [num_tokens, num_heads, head_size]      strides (q|o)_stride_t / _h, innermost contiguous
+ *   key, value     [num_tokens, num_kv_heads, head_size]   strides (k|v)_stride_t / _h, 16-byte aligned rows
+ *   key_cache      [num_blocks, num_kv_heads, head_size/8, block_size, 8]   (16-bit cache, x = 8)
+ *   value_cache    [num_blocks, num_kv_heads, head_size, block_size]
+ *   block_tables   [batch, block_table_stride] int32; start_loc, seq_lens, ctx_lens [batch] int32
+ * head_size: any multiple of 8 up to 256; block_size: any power of two >= 8; dtype f16 | bf16;
+ * kv_dtype must be B200PA_KV_AUTO (the reference's fp8 branch here is e5m2-bitcast-only and documented
+ * as broken, vllm/attention/backends/xformers.py:301-304).
+ */
+typedef struct {
+  void* out;
+  const void* query;
+  const void* key;
+  const void* value;
+  const void* key_cache;
+  const void* value_cache;
+  const int32_t* block_tables;
+  const int32_t* start_loc;
+  const int32_t* seq_lens;
+  const int32_t* ctx_lens;
+  const float* alibi_slopes; /* nullable, [num_heads] */
+  int64_t q_stride_t, q_stride_h;
+  int64_t k_stride_t, k_stride_h;
+  int64_t v_stride_t, v_stride_h;
+  int64_t o_stride_t, o_stride_h;
+  int64_t kc_block_stride, kc_head_stride; /* key_cache.stride(0), .stride(1), elements */
+  int64_t vc_block_stride, vc_head_stride; /* value_cache.stride(0), .stride(1), elements */
+  int64_t block_table_stride;
+  int32_t batch;
+  int32_t max_query_len; /* the reference's max_input_len: upper bound of q_len over the batch */
+  int32_t num_heads;
+  int32_t num_kv_heads;
+  int32_t head_size;
+  int32_t block_size;
+  int32_t sliding_window; /* <= 0 disables */
+  int32_t dtype;          /* b200pa_dtype_t */
+  int32_t kv_dtype;       /* b200pa_kv_dtype_t */
+  float scale;            /* the reference uses 1/sqrt(head_size) (:706) */
+} b200pa_prefill_params_t;
+
+int b200pa_context_attention_fwd(const b200pa_prefill_params_t* p, b200pa_stream_t stream);
+
+/*
  * copy_blocks
  * replaces: csrc/cache.h:11-13, csrc/cache_kernels.cu:68-146.
  *   key_cache_ptrs / value_cache_ptrs : HOST arrays of num_layers device pointers

@@ -14,7 +14,9 @@ Both are bound through the small pybind shims in this directory
 (ref_cpu_shim.cpp, ref_cuda_shim.cpp).  The reference's own build system
 (CMake + network-fetched CUTLASS + torch 2.3 pin) is not run.
 
-Usage: python oracle/build_ref.py [cpu] [cuda] [--force]
+  prefix_prefill_ref.py          vllm/attention/ops/prefix_prefill.py staged verbatim (Triton; runs on the GPU box)
+
+Usage: python oracle/build_ref.py [cpu] [cuda] [prefill] [--force]
 """
 import os
 import subprocess
@@ -118,6 +120,18 @@ def build_cuda(force=False):
           "-lc10_cuda", "-ltorch_python", "-L/usr/local/cuda/lib64", "-lcudart"])
 
 
+def stage_prefix_prefill():
+    """The reference's prefix-prefill is a Triton (Python) module: it cannot be compiled here, and it needs a
+    GPU to run.  Stage it VERBATIM into oracle/_ref/ (git-ignored, so it never enters the repo history, but it
+    travels to the GPU box like the compiled reference objects) so that tests/test_gpu_prefill.py and
+    tools/bench_prefill.py can run the reference's own kernels beside ours."""
+    import shutil
+    src = os.path.join(REF, "vllm", "attention", "ops", "prefix_prefill.py")
+    os.makedirs(OUT, exist_ok=True)
+    shutil.copyfile(src, os.path.join(OUT, "prefix_prefill_ref.py"))
+    print("staged", src)
+
+
 def main():
     if not os.path.isdir(CSRC):
         print(f"{REF} not present: keeping prebuilt oracle/_ref as is")
@@ -129,6 +143,8 @@ def main():
         build_cpu(force)
     if "cuda" in args:
         build_cuda(force)
+    if "prefill" in args or "cuda" in args:
+        stage_prefix_prefill()
     print(f"done in {time.time() - t0:.0f}s")
     return 0
 

@@ -201,3 +201,26 @@ def convert_fp8(output, input, scale: float = 1.0, kv_dtype: str = "fp8") -> Non
 
 def float_to_fp8(x: float, kv_dtype: str = "fp8") -> int:
     return int(lib().oracle_float_to_fp8(ctypes.c_float(x), KV[kv_dtype]))
+
+
+def context_attention_fwd(q, k, v, o, k_cache, v_cache, b_loc, b_start_loc, b_seq_len, b_ctx_len, max_input_len,
+                          alibi_slopes=None, sliding_window=None) -> None:
+    """Restatement of the reference's Triton prefix-prefill kernels (prefix_prefill.py:10-245, 442-681)."""
+    for t in (q, k, v, o, k_cache, v_cache):
+        assert _cpu(t).is_contiguous() and t.dtype == q.dtype
+    assert k_cache.shape[-1] == 8, "16-bit cache layout (x = 8)"
+    loc = _cpu(b_loc).to(torch.int32).contiguous()
+    start = _cpu(b_start_loc).to(torch.int32).contiguous()
+    seql = _cpu(b_seq_len).to(torch.int32).contiguous()
+    ctxl = _cpu(b_ctx_len).to(torch.int32).contiguous()
+    slopes = _cpu(alibi_slopes).to(torch.float32).contiguous() if alibi_slopes is not None else None
+    f = lib().oracle_context_attention_fwd
+    f.restype = ctypes.c_int
+    f.argtypes = [ctypes.c_void_p] * 7 + [ctypes.c_int64] + [ctypes.c_void_p] * 3 + [ctypes.c_int] * 5 + \
+        [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+    rc = f(o.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+           loc.data_ptr(), loc.stride(0), start.data_ptr(), seql.data_ptr(), ctxl.data_ptr(), seql.shape[0],
+           q.shape[1], k.shape[1], q.shape[2], v_cache.shape[3],
+           slopes.data_ptr() if slopes is not None else None,
+           int(sliding_window) if sliding_window else 0, DT[q.dtype])
+    assert rc == 0

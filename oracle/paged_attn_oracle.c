@@ -444,3 +444,122 @@ int oracle_paged_attention_v2(void* out, float* exp_sums, float* max_logits, voi
   free(o);
   return 0;
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * context_attention_fwd (prefix-prefill attention over the paged cache) — restates the reference's
+ * Triton kernels row by row with their own tile order and rounding points:
+ *   vllm/attention/ops/prefix_prefill.py:10-245  (_fwd_kernel: normalised accumulator, window -> -10000)
+ *   vllm/attention/ops/prefix_prefill.py:442-681 (_fwd_kernel_alibi: un-normalised accumulator, no window)
+ *   BLOCK_M = BLOCK_N = 128 (:698-699), sm_scale = 1/sqrt(D) (:706), p rounded to the value dtype before
+ *   tl.dot (:170, :236, :596, :667), fp32 accumulation.
+ * k_cache [nb, Hkv, D/8, B, 8], v_cache [nb, Hkv, D, B] of dtype dt; q/k/v/out [tokens, heads, D] contiguous.
+ * --------------------------------------------------------------------------------------------- */
+int oracle_context_attention_fwd(void* out, const void* q, const void* k, const void* v, const void* k_cache,
+                                 const void* v_cache, const int32_t* b_loc, int64_t b_loc_stride,
+                                 const int32_t* b_start_loc, const int32_t* b_seq_len, const int32_t* b_ctx_len,
+                                 int batch, int num_heads, int num_kv_heads, int D, int block_size,
+                                 const float* alibi_slopes, int sliding_window, int dt) {
+  enum { BLK = 128 };
+  if (dt != DT_F16 && dt != DT_BF16 && dt != DT_F32) return -1;
+  const float sm_scale = 1.0f / sqrtf((float)D);
+  const int qpk = num_heads / num_kv_heads;
+  const int x = 8;
+  float* kt = (float*)malloc(sizeof(float) * BLK * D);
+  float* vt = (float*)malloc(sizeof(float) * BLK * D);
+  float* acc = (float*)malloc(sizeof(float) * D);
+  float* qrow = (float*)malloc(sizeof(float) * D);
+  float qk[BLK], pr[BLK];
+  const int W = alibi_slopes ? 0 : (sliding_window > 0 ? sliding_window : 0);
+  for (int b = 0; b < batch; ++b) {
+    const int ctx = b_ctx_len[b], qlen = b_seq_len[b] - ctx;
+    const int64_t t0 = b_start_loc[b];
+    for (int h = 0; h < num_heads; ++h) {
+      const int kvh = h / qpk;
+      for (int m = 0; m < qlen; ++m) {
+        for (int d = 0; d < D; ++d) { qrow[d] = load_elem(q, ((t0 + m) * num_heads + h) * D + d, dt); acc[d] = 0.f; }
+        float m_i = -INFINITY, l_i = 0.f;
+        const int start_m = m / BLK;
+        const int n_ctx_tiles = (ctx + BLK - 1) / BLK;
+        const int n_new_tiles = start_m + 1; /* range(0, (start_m + 1) * BLOCK_M, BLOCK_N) (:193, :615) */
+        for (int tile = 0; tile < n_ctx_tiles + n_new_tiles; ++tile) {
+          const int is_ctx = tile < n_ctx_tiles;
+          const int start_n = (is_ctx ? tile : tile - n_ctx_tiles) * BLK;
+          /* gather the K / V tile as the masked tl.load would (other = 0) */
+          for (int n = 0; n < BLK; ++n) {
+            const int pos = start_n + n;
+            const int valid = is_ctx ? (pos < ctx) : (pos < qlen);
+            for (int d = 0; d < D; ++d) {
+              float kv = 0.f, vv = 0.f;
+              if (valid && is_ctx) {
+                const int64_t blk = b_loc[b * b_loc_stride + pos / block_size];
+                const int o = pos % block_size;
+                kv = load_elem(k_cache, (((blk * num_kv_heads + kvh) * (D / x) + d / x) * block_size + o) * x + d % x, dt);
+                vv = load_elem(v_cache, ((blk * num_kv_heads + kvh) * D + d) * block_size + o, dt);
+              } else if (valid) {
+                kv = load_elem(k, ((t0 + pos) * num_kv_heads + kvh) * D + d, dt);
+                vv = load_elem(v, ((t0 + pos) * num_kv_heads + kvh) * D + d, dt);
+              }
+              kt[n * D + d] = kv;
+              vt[n * D + d] = vv;
+            }
+          }
+          float m_ij = -INFINITY;
+          for (int n = 0; n < BLK; ++n) {
+            const int pos = start_n + n;
+            float s = 0.f;
+            for (int d = 0; d < D; ++d) s += qrow[d] * kt[n * D + d];
+            if (is_ctx) {
+              s = (pos < ctx) ? s : -INFINITY;
+              s *= sm_scale;
+              if (W > 0 && !((ctx + m) - pos < W)) s = -10000.f;                      /* :141-143 */
+            } else {
+              s *= sm_scale;
+              s = (m >= pos) ? s : -INFINITY;                                          /* :207-208 */
+              if (W > 0 && !(m - pos < W)) s = -10000.f;                              /* :209-212 */
+            }
+            if (alibi_slopes) {                                                        /* :560-565, :633-638 */
+              const float qpos = (float)(ctx + m), kpos = (float)((is_ctx ? 0 : ctx) + pos);
+              float a = (kpos - qpos) * alibi_slopes[h];
+              if (!(a <= 0.f)) a = -INFINITY;
+              s += a;
+            }
+            qk[n] = s;
+            if (s > m_ij) m_ij = s;
+          }
+          if (alibi_slopes) {
+            const float m_new = fmaxf(m_i, m_ij);
+            float l_ij = 0.f;
+            for (int n = 0; n < BLK; ++n) { pr[n] = expf(qk[n] - m_new); l_ij += pr[n]; }
+            const float alpha = expf(m_i - m_new);
+            for (int d = 0; d < D; ++d) acc[d] *= alpha;
+            for (int n = 0; n < BLK; ++n) {
+              const float pn = round_to(pr[n], dt);
+              if (pn != 0.f) for (int d = 0; d < D; ++d) acc[d] += pn * vt[n * D + d];
+            }
+            l_i = alpha * l_i + l_ij;
+            m_i = m_new;
+          } else {
+            float l_ij = 0.f;
+            for (int n = 0; n < BLK; ++n) { pr[n] = expf(qk[n] - m_ij); l_ij += pr[n]; }
+            const float m_new = fmaxf(m_i, m_ij);
+            const float alpha = expf(m_i - m_new), beta = expf(m_ij - m_new);
+            const float l_new = alpha * l_i + beta * l_ij;
+            const float p_scale = beta / l_new;
+            const float acc_scale = l_i / l_new * alpha;
+            for (int d = 0; d < D; ++d) acc[d] *= acc_scale;
+            for (int n = 0; n < BLK; ++n) {
+              const float pn = round_to(pr[n] * p_scale, dt);
+              if (pn != 0.f) for (int d = 0; d < D; ++d) acc[d] += pn * vt[n * D + d];
+            }
+            l_i = l_new;
+            m_i = m_new;
+          }
+        }
+        for (int d = 0; d < D; ++d)
+          store_elem(out, ((t0 + m) * num_heads + h) * D + d, dt, alibi_slopes ? acc[d] / l_i : acc[d]);
+      }
+    }
+  }
+  free(kt); free(vt); free(acc); free(qrow);
+  return 0;
+}

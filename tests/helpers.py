@@ -159,3 +159,98 @@ def make_block_tables(num_seqs: int, max_num_blocks_per_seq: int, num_blocks: in
                 for i in range(num_seqs)]
     return [[rng.randint(0, num_blocks - 1) for _ in range(max_num_blocks_per_seq)]
             for _ in range(num_seqs)]
+
+
+# ---------------------------------------------------------------------------------------------------
+# prefix-prefill (context_attention_fwd) fixtures — tests/kernels/test_prefix_prefill.py:50-124
+# ---------------------------------------------------------------------------------------------------
+def make_prefill_case(num_heads: int, num_queries_per_kv: int, head_size: int, dtype: torch.dtype, device: str,
+                      batch: int = 10, max_q: int = 1024, max_ctx: int = 1024, block_size: int = 32, seed: int = 0,
+                      amplitude: float = 1e-3, min_len: int = 16, query_lens=None, ctx_lens=None, stale_nan=False):
+    """Inputs of the reference's test: ragged query/context lengths, the context scattered into a paged cache
+    through a random block table, K cache [nb, H, D/8, B, 8], V cache [nb, H, D, B]."""
+    rng = random.Random(seed)
+    g = torch.Generator().manual_seed(seed)
+    query_lens = query_lens or [rng.randint(min_len, max_q) for _ in range(batch)]
+    ctx_lens = ctx_lens if ctx_lens is not None else [rng.randint(min_len, max_ctx) for _ in range(batch)]
+    batch = len(query_lens)
+    seq_lens = [a + b for a, b in zip(query_lens, ctx_lens)]
+    num_kv_heads = num_heads // num_queries_per_kv
+    max_block_per_request = max(1, (max(ctx_lens) + block_size - 1) // block_size)
+    cache_size = batch * max_block_per_request
+    num_tokens = sum(query_lens)
+    query = torch.empty(num_tokens, num_heads, head_size, dtype=torch.float32).uniform_(-amplitude, amplitude, generator=g)
+    kv = torch.empty(sum(seq_lens), 2, num_kv_heads, head_size, dtype=torch.float32).uniform_(-amplitude, amplitude, generator=g)
+    query, kv = query.to(dtype), kv.to(dtype)
+    key, value = kv.unbind(dim=1)
+    fill = float("nan") if stale_nan else 0.0
+    k_cache = torch.full((cache_size, block_size, num_kv_heads, head_size), fill, dtype=dtype)
+    v_cache = torch.full((cache_size, block_size, num_kv_heads, head_size), fill, dtype=dtype)
+    k = torch.zeros(num_tokens, num_kv_heads, head_size, dtype=dtype)
+    v = torch.zeros(num_tokens, num_kv_heads, head_size, dtype=dtype)
+    block_table = torch.randperm(cache_size, generator=g).view(batch, max_block_per_request)
+    b_start_loc = torch.cumsum(torch.tensor([0] + query_lens[:-1]), dim=0)
+    b_seq_start_loc = torch.cumsum(torch.tensor([0] + seq_lens[:-1]), dim=0)
+    for i in range(batch):
+        s, c, ql = int(b_seq_start_loc[i]), ctx_lens[i], query_lens[i]
+        k[int(b_start_loc[i]):int(b_start_loc[i]) + ql] = key[s + c:s + c + ql]
+        v[int(b_start_loc[i]):int(b_start_loc[i]) + ql] = value[s + c:s + c + ql]
+        for blk in range((c + block_size - 1) // block_size):
+            n = min(block_size, c - blk * block_size)
+            phys = int(block_table[i, blk])
+            k_cache[phys, :n] = key[s + blk * block_size:s + blk * block_size + n]
+            v_cache[phys, :n] = value[s + blk * block_size:s + blk * block_size + n]
+    k_cache = k_cache.view(-1, block_size, num_kv_heads, head_size // 8, 8).permute(0, 2, 3, 1, 4).contiguous()
+    v_cache = v_cache.view(-1, block_size, num_kv_heads, head_size).permute(0, 2, 3, 1).contiguous()
+    case = dict(query=query, k=k, v=v, k_cache=k_cache, v_cache=v_cache, block_table=block_table.to(torch.int32),
+                b_start_loc=b_start_loc.to(torch.int32), b_seq_len=torch.tensor(seq_lens, dtype=torch.int32),
+                b_ctx_len=torch.tensor(ctx_lens, dtype=torch.int32), key_full=key.contiguous(),
+                value_full=value.contiguous())
+    case = {n: t.to(device) for n, t in case.items()}
+    case.update(query_lens=query_lens, ctx_lens=ctx_lens, seq_lens=seq_lens, max_input_len=max(query_lens),
+                num_kv_heads=num_kv_heads)
+    return case
+
+
+def ref_context_attention(case, alibi_slopes: Optional[torch.Tensor] = None, sliding_window: int = 0,
+                          scale: Optional[float] = None) -> torch.Tensor:
+    """fp32 dense masked attention per sequence over the un-paged keys/values (what xformers'
+    BlockDiagonalCausalFromBottomRightMask [+ local attention] computes in the reference's test, :160-186)."""
+    query, key, value = case["query"], case["key_full"], case["value_full"]
+    T, H, D = query.shape
+    Hkv = key.shape[1]
+    scale = scale if scale is not None else 1.0 / (D ** 0.5)
+    out = torch.empty(T, H, D, dtype=torch.float32, device=query.device)
+    qs = ss = 0
+    for ql, sl in zip(case["query_lens"], case["seq_lens"]):
+        q = query[qs:qs + ql].float().transpose(0, 1)                               # [H, ql, D]
+        kk = key[ss:ss + sl].float().repeat_interleave(H // Hkv, dim=1).transpose(0, 1)   # [H, sl, D]
+        vv = value[ss:ss + sl].float().repeat_interleave(H // Hkv, dim=1).transpose(0, 1)
+        logits = torch.matmul(q, kk.transpose(1, 2)) * scale                        # [H, ql, sl]
+        qpos = torch.arange(sl - ql, sl, device=query.device)[:, None]
+        kpos = torch.arange(sl, device=query.device)[None, :]
+        mask = kpos <= qpos
+        if alibi_slopes is not None:
+            logits = logits + alibi_slopes.float()[:, None, None] * (kpos - qpos).float()[None]
+        elif sliding_window and sliding_window > 0:
+            mask = mask & (qpos - kpos < sliding_window)
+        logits = logits.masked_fill(~mask[None], float("-inf"))
+        out[qs:qs + ql] = torch.matmul(torch.softmax(logits, dim=-1), vv).transpose(0, 1)
+        qs += ql
+        ss += sl
+    return out
+
+
+def load_ref_prefix_prefill():
+    """The reference's own Triton prefix-prefill module, when oracle/build_ref.py staged it under oracle/_ref/
+    (git-ignored; test infrastructure only) and Triton + a GPU are available; else None."""
+    path = os.path.join(REF_DIR, "prefix_prefill_ref.py")
+    if not os.path.exists(path) or not torch.cuda.is_available():
+        return None
+    try:
+        spec = importlib.util.spec_from_file_location("prefix_prefill_ref", path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        return mod
+    except Exception:  # noqa: BLE001 - an incompatible Triton just means "no reference run"
+        return None

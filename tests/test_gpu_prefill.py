@@ -1,0 +1,168 @@
+"""GPU parity of context_attention_fwd (csrc/prefill.cu via the C-ABI b200pa_context_attention_fwd) on the
+reference's own test grid (tests/kernels/test_prefix_prefill.py:13-60, 214-262) plus what it does not cover:
+bf16, block sizes 8/16/32/128, realistic magnitudes, empty prefix, stale NaN bits behind ctx_len, strided q/k/v.
+Checkers: fp32 dense attention (the xformers computation of the reference test), the CPU oracle restating the
+Triton kernels, and — when staged under oracle/_ref/ — the reference's Triton kernels themselves.
+"""
+import math
+
+import pytest
+import torch
+
+from tests import helpers
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+NUM_HEADS = [64]
+NUM_QUERIES_PER_KV = [1, 8, 64]
+HEAD_SIZES = [128, 96, 24]
+SLIDING_WINDOW = [0, 16, 64, 128, 256, 512, 2048]
+
+
+def _run(ops, case, slopes=None, window=None):
+    out = torch.full_like(case["query"], float("nan"))
+    ops.context_attention_fwd(case["query"], case["k"], case["v"], out, case["k_cache"], case["v_cache"],
+                              case["block_table"], case["b_start_loc"], case["b_seq_len"], case["b_ctx_len"],
+                              case["max_input_len"], slopes, window)
+    torch.cuda.synchronize()
+    return out
+
+
+def _alibi_slopes(total_num_heads: int) -> torch.Tensor:
+    """bloom-style slopes, as the reference test builds them (test_prefix_prefill.py:239-262)."""
+    p2 = 2 ** math.floor(math.log2(total_num_heads))
+    base = 2 ** (-(2 ** -(math.log2(p2) - 3)))
+    slopes = [base ** i for i in range(1, p2 + 1)]
+    if p2 != total_num_heads:
+        extra = 2 ** (-(2 ** -(math.log2(2 * p2) - 3)))
+        slopes += [extra ** i for i in range(1, 1 + 2 * min(p2, total_num_heads - p2), 2)]
+    return torch.tensor(slopes, dtype=torch.float32)
+
+
+@pytest.mark.parametrize("num_heads", NUM_HEADS)
+@pytest.mark.parametrize("num_queries_per_kv", NUM_QUERIES_PER_KV)
+@pytest.mark.parametrize("head_size", HEAD_SIZES)
+@pytest.mark.parametrize("sliding_window", SLIDING_WINDOW)
+@torch.inference_mode()
+def test_contexted_kv_attention_reference_grid(ops, num_heads, num_queries_per_kv, head_size, sliding_window):
+    """The reference's test verbatim: fp16, U(-1e-3, 1e-3), block 32, atol 1e-6 (:211)."""
+    case = helpers.make_prefill_case(num_heads, num_queries_per_kv, head_size, torch.float16, DEV)
+    out = _run(ops, case, None, sliding_window)
+    ref = helpers.ref_context_attention(case, None, sliding_window)
+    assert torch.allclose(ref, out.float(), atol=1e-6, rtol=0)
+
+
+@pytest.mark.parametrize("num_queries_per_kv", NUM_QUERIES_PER_KV)
+@pytest.mark.parametrize("head_size", HEAD_SIZES)
+@torch.inference_mode()
+def test_contexted_kv_attention_alibi_reference_grid(ops, num_queries_per_kv, head_size):
+    case = helpers.make_prefill_case(64, num_queries_per_kv, head_size, torch.float16, DEV)
+    slopes = _alibi_slopes(64).to(DEV)
+    out = _run(ops, case, slopes, None)
+    ref = helpers.ref_context_attention(case, slopes, 0)
+    assert torch.allclose(ref, out.float(), atol=1e-6, rtol=0)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("head_size", [64, 80, 96, 112, 128, 192, 256, 24])
+@pytest.mark.parametrize("block_size", [8, 16, 32, 128])
+@pytest.mark.parametrize("mode", ["plain", "window", "alibi"])
+@torch.inference_mode()
+def test_realistic_magnitudes(ops, dtype, head_size, block_size, mode):
+    """U(-1, 1) inputs: logits O(1), so masks, softmax and the p rounding actually matter."""
+    case = helpers.make_prefill_case(16, 4, head_size, dtype, DEV, batch=6, max_q=300, max_ctx=400,
+                                     block_size=block_size, amplitude=1.0, min_len=1, seed=block_size + head_size,
+                                     stale_nan=True)
+    slopes = _alibi_slopes(16).to(DEV) if mode == "alibi" else None
+    window = 100 if mode == "window" else 0
+    out = _run(ops, case, slopes, window)
+    ref = helpers.ref_context_attention(case, slopes, window)
+    assert not torch.isnan(out).any()
+    atol = 1e-3 if dtype == torch.float16 else 4e-3   # north_star: atol 1e-3 / rtol 1e-2 for 16-bit types
+    torch.testing.assert_close(out.float(), ref, atol=atol, rtol=1e-2)
+
+
+@pytest.mark.parametrize("mode", ["plain", "window", "alibi"])
+@torch.inference_mode()
+def test_vs_cpu_oracle(ops, oracle, mode):
+    case = helpers.make_prefill_case(8, 2, 64, torch.float16, DEV, query_lens=[70, 1, 200, 129],
+                                     ctx_lens=[130, 300, 0, 31], block_size=16, amplitude=1.0)
+    slopes = _alibi_slopes(8) if mode == "alibi" else None
+    window = 77 if mode == "window" else 0
+    out = _run(ops, case, slopes.to(DEV) if slopes is not None else None, window)
+    cpu = {n: (t.cpu() if torch.is_tensor(t) else t) for n, t in case.items()}
+    exp = torch.empty_like(cpu["query"])
+    oracle.context_attention_fwd(cpu["query"], cpu["k"], cpu["v"], exp, cpu["k_cache"], cpu["v_cache"],
+                                 cpu["block_table"], cpu["b_start_loc"], cpu["b_seq_len"], cpu["b_ctx_len"],
+                                 cpu["max_input_len"], slopes, window)
+    torch.testing.assert_close(out.cpu().float(), exp.float(), atol=1e-3, rtol=1e-2)
+
+
+@pytest.mark.parametrize("sliding_window", [0, 64, 2048])
+@pytest.mark.parametrize("alibi", [False, True])
+@torch.inference_mode()
+def test_vs_reference_triton(ops, sliding_window, alibi):
+    """The reference's Triton kernels run beside ours (only when oracle/build_ref.py staged the module)."""
+    ref_mod = helpers.load_ref_prefix_prefill()
+    if ref_mod is None:
+        pytest.skip("oracle/_ref/prefix_prefill_ref.py not staged or Triton unusable")
+    if alibi and sliding_window:
+        pytest.skip("the reference's ALiBi kernel has no window")
+    case = helpers.make_prefill_case(32, 4, 128, torch.float16, DEV, amplitude=1.0)
+    slopes = _alibi_slopes(32).to(DEV) if alibi else None
+    out = _run(ops, case, slopes, sliding_window)
+    exp = torch.empty_like(case["query"])
+    try:
+        ref_mod.context_attention_fwd(case["query"], case["k"], case["v"], exp, case["k_cache"], case["v_cache"],
+                                      case["block_table"], case["b_start_loc"], case["b_seq_len"], case["b_ctx_len"],
+                                      case["max_input_len"], slopes, sliding_window)
+        torch.cuda.synchronize()
+    except Exception as e:  # noqa: BLE001
+        pytest.skip(f"reference Triton kernel does not run with this Triton: {type(e).__name__}")
+    torch.testing.assert_close(out.float(), exp.float(), atol=1e-3, rtol=1e-2)
+
+
+@torch.inference_mode()
+def test_int64_index_tensors_and_strided_inputs(ops):
+    """The reference test passes int64 block tables / lengths (:83-90); vLLM passes q/k/v as slices of a fused qkv."""
+    case = helpers.make_prefill_case(16, 4, 128, torch.float16, DEV, batch=4, max_q=200, max_ctx=200, amplitude=1.0)
+    ref = helpers.ref_context_attention(case)
+    T = case["query"].shape[0]
+    qkv = torch.empty(T, (16 + 4 + 4) * 128, dtype=torch.float16, device=DEV)
+    qkv[:, :16 * 128] = case["query"].reshape(T, -1)
+    qkv[:, 16 * 128:20 * 128] = case["k"].reshape(T, -1)
+    qkv[:, 20 * 128:] = case["v"].reshape(T, -1)
+    q, k, v = qkv.split([16 * 128, 4 * 128, 4 * 128], dim=-1)
+    out = torch.empty(T, 16, 128, dtype=torch.float16, device=DEV)
+    ops.context_attention_fwd(q.view(T, 16, 128), k.view(T, 4, 128), v.view(T, 4, 128), out, case["k_cache"],
+                              case["v_cache"], case["block_table"].long(), case["b_start_loc"].long(),
+                              case["b_seq_len"].long(), case["b_ctx_len"].long(), case["max_input_len"])
+    torch.testing.assert_close(out.float(), ref, atol=1e-3, rtol=1e-2)
+
+
+@torch.inference_mode()
+def test_forward_prefix_helper(ops):
+    """PagedAttention.forward_prefix (paged_attn.py:185-216) end to end, query_start_loc of batch + 1 entries."""
+    from vllm_legacy_b200.attention.ops.paged_attn import PagedAttention
+    case = helpers.make_prefill_case(8, 1, 128, torch.bfloat16, DEV, batch=3, max_q=150, max_ctx=150, amplitude=1.0,
+                                     block_size=16)
+    qsl = torch.cat([case["b_start_loc"], torch.tensor([case["query"].shape[0]], dtype=torch.int32, device=DEV)])
+    out = PagedAttention.forward_prefix(case["query"], case["k"], case["v"], case["k_cache"], case["v_cache"],
+                                        case["block_table"], qsl, case["b_seq_len"], case["b_ctx_len"],
+                                        case["max_input_len"], None, None)
+    torch.testing.assert_close(out.float(), helpers.ref_context_attention(case), atol=4e-3, rtol=1e-2)
+
+
+@torch.inference_mode()
+def test_errors(ops):
+    case = helpers.make_prefill_case(8, 1, 128, torch.float16, DEV, batch=2, max_q=32, max_ctx=32)
+    out = torch.empty_like(case["query"])
+    with pytest.raises(RuntimeError):   # fp32 is not a tensor-core input type of this kernel
+        ops.context_attention_fwd(case["query"].float(), case["k"].float(), case["v"].float(), out.float(),
+                                  case["k_cache"].float(), case["v_cache"].float(), case["block_table"],
+                                  case["b_start_loc"], case["b_seq_len"], case["b_ctx_len"], 32)
+    with pytest.raises(RuntimeError):   # CPU tensors: no CPU path
+        ops.context_attention_fwd(case["query"].cpu(), case["k"].cpu(), case["v"].cpu(), out.cpu(),
+                                  case["k_cache"].cpu(), case["v_cache"].cpu(), case["block_table"].cpu(),
+                                  case["b_start_loc"].cpu(), case["b_seq_len"].cpu(), case["b_ctx_len"].cpu(), 32)

@@ -110,8 +110,46 @@ def test_backend_impl_decode_path(recorder):
     assert [c[0] for c in recorder.calls] == ["reshape_and_cache", "paged_attention_v1"]
     with pytest.raises(ValueError):
         B200PagedAttentionBackend.get_impl_cls()(8, 100, 1.0)
-    with pytest.raises(NotImplementedError):
-        PagedAttention.forward_prefix()
+
+
+def test_backend_impl_mixed_prefill_decode(recorder):
+    """Prefill rows first, then decode rows; metadata split like XFormersMetadata (xformers.py:120-177);
+    prompts with a cached prefix go to context_attention_fwd, decode rows to paged attention."""
+    Hq, Hkv, D, B, nb = 8, 2, 64, 16, 8
+    impl = B200PagedAttentionBackend.get_impl_cls()(Hq, D, 0.125, Hkv, None, None, "auto")
+    # 2 prompts (5 and 3 new tokens, contexts 16 and 0) + 2 decode rows
+    meta = B200PagedAttentionBackend.make_metadata(
+        num_prefills=2, num_prefill_tokens=8, num_decode_tokens=2, slot_mapping=torch.arange(10),
+        seq_lens=[21, 3, 7, 9], seq_lens_tensor=torch.tensor([21, 3, 7, 9], dtype=torch.int32),
+        max_query_len=5, max_prefill_seq_len=21, max_decode_seq_len=9,
+        query_start_loc=torch.tensor([0, 5, 8, 9, 10], dtype=torch.int32), seq_start_loc=None,
+        context_lens_tensor=torch.tensor([16, 0, 6, 8], dtype=torch.int32),
+        block_tables=torch.arange(8, dtype=torch.int32).view(4, 2), use_cuda_graph=False)
+    pm, dm = meta.prefill_metadata, meta.decode_metadata
+    assert pm.num_prefills == 2 and pm.num_decode_tokens == 0 and pm.seq_lens == [21, 3]
+    assert pm.query_start_loc.tolist() == [0, 5, 8] and pm.context_lens_tensor.tolist() == [16, 0]
+    assert pm.block_tables.tolist() == [[0, 1], [2, 3]] and pm.slot_mapping.tolist() == list(range(8))
+    assert dm.num_prefills == 0 and dm.seq_lens_tensor.tolist() == [7, 9] and dm.block_tables.tolist() == [[4, 5], [6, 7]]
+    assert dm.slot_mapping.tolist() == [8, 9] and dm.max_decode_seq_len == 9
+    assert meta.prefill_metadata is pm and meta.decode_metadata is dm   # cached
+    kv_cache = torch.zeros(*B200PagedAttentionBackend.get_kv_cache_shape(nb, B, Hkv, D))
+    out = impl.forward(torch.zeros(10, Hq * D), torch.zeros(10, Hkv * D), torch.zeros(10, Hkv * D), kv_cache, meta, 1.0)
+    assert out.shape == (10, Hq * D)
+    assert [c[0] for c in recorder.calls] == ["reshape_and_cache", "context_attention_fwd", "paged_attention_v1"]
+    pf = recorder.calls[1][1]
+    assert pf[0].shape == (8, Hq, D) and pf[1].shape == (8, Hkv, D) and pf[3].shape == (8, Hq, D)
+    assert pf[7].tolist() == [0, 5] and pf[8].tolist() == [21, 3] and pf[9].tolist() == [16, 0] and pf[10] == 5
+    assert recorder.calls[2][1][1].shape == (2, Hq, D)
+    # prompt run without any cache (profiling run): plain causal attention = the same kernel with context 0
+    recorder.calls.clear()
+    meta2 = B200PagedAttentionBackend.make_metadata(
+        num_prefills=2, num_prefill_tokens=8, num_decode_tokens=0, slot_mapping=torch.arange(8),
+        seq_lens=[5, 3], seq_lens_tensor=torch.tensor([5, 3], dtype=torch.int32), max_query_len=5,
+        max_prefill_seq_len=5, max_decode_seq_len=0, query_start_loc=torch.tensor([0, 5, 8], dtype=torch.int32),
+        context_lens_tensor=torch.zeros(2, dtype=torch.int32), block_tables=torch.zeros(2, 0, dtype=torch.int32))
+    impl.forward(torch.zeros(8, Hq * D), torch.zeros(8, Hkv * D), torch.zeros(8, Hkv * D), None, meta2, 1.0)
+    (name, args, _), = recorder.calls
+    assert name == "context_attention_fwd" and args[8].tolist() == [5, 3] and args[9].tolist() == [0, 0]
 
 
 def test_shard_heads_matches_reference_rules():

@@ -324,3 +324,23 @@ def test_oracle_rotary_embedding_vs_native(oracle, is_neox, dtype, head_size, ro
         torch.testing.assert_close(k.view(T, Hkv, head_size), want_k, atol=1e-6, rtol=1e-6)
     else:
         assert torch.equal(q.view(T, H, head_size), want_q) and torch.equal(k.view(T, Hkv, head_size), want_k)
+
+
+# ---------------------------------------------------------------------------------------------------
+# context_attention_fwd oracle (prefix_prefill.py restatement) vs independent fp32 dense attention
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("mode", ["plain", "window", "alibi"])
+def test_oracle_context_attention_vs_dense(oracle, dtype, mode):
+    from tests import helpers
+    case = helpers.make_prefill_case(num_heads=4, num_queries_per_kv=2, head_size=32, dtype=dtype, device="cpu",
+                                     query_lens=[5, 150, 37], ctx_lens=[200, 17, 0], block_size=16, amplitude=1.0)
+    slopes = torch.tensor([0.5, 0.25, 0.125, 0.0625]) if mode == "alibi" else None
+    window = 48 if mode == "window" else 0
+    out = torch.empty_like(case["query"])
+    oracle.context_attention_fwd(case["query"], case["k"], case["v"], out, case["k_cache"], case["v_cache"],
+                                 case["block_table"], case["b_start_loc"], case["b_seq_len"], case["b_ctx_len"],
+                                 case["max_input_len"], slopes, window)
+    ref = helpers.ref_context_attention(case, slopes, window)
+    tol = {torch.float16: 2e-3, torch.bfloat16: 1e-2, torch.float32: 1e-5}[dtype]
+    torch.testing.assert_close(out.float(), ref, atol=tol, rtol=1e-2)

@@ -104,6 +104,16 @@ def rotary_embedding_reshape_and_cache(positions: torch.Tensor, query: torch.Ten
         slot_mapping, kv_cache_dtype, kv_scale)
 
 
+# prefix-prefill attention (vllm/attention/ops/prefix_prefill.py:684-696)
+def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: torch.Tensor,
+                          k_cache: torch.Tensor, v_cache: torch.Tensor, b_loc: torch.Tensor,
+                          b_start_loc: torch.Tensor, b_seq_len: torch.Tensor, b_ctx_len: torch.Tensor,
+                          max_input_len: int, alibi_slopes: Optional[torch.Tensor] = None,
+                          sliding_window: Optional[int] = None) -> None:
+    vllm_ops.context_attention_fwd(q, k, v, o, k_cache, v_cache, b_loc, b_start_loc, b_seq_len, b_ctx_len,
+                                   max_input_len, alibi_slopes, sliding_window)
+
+
 # cache ops
 def reshape_and_cache(
     key: torch.Tensor,

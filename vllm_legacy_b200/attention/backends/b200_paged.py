@@ -2,10 +2,10 @@
 route decode through `PagedAttention` (`vllm/attention/backends/xformers.py:19-58, 196-335`;
 the fork's `hip.py:166-174, 306-319` dense path; `blocksparse_attn.py:357-390`).
 
-It writes the step's K/V into the paged cache (`reshape_and_cache`) and runs decode attention
-(`paged_attention_v1/v2`) on the B200 kernels.  Prefill attention (xformers / flash / HiP Triton) is
-third-party code outside this path: a batch that contains prefill tokens still gets its K/V cached,
-and the prefill rows of the output are left to the caller's prefill implementation.
+It writes the step's K/V into the paged cache (`reshape_and_cache`), runs decode attention
+(`paged_attention_v1/v2`) and prefill attention — with or without a cached prefix — on the B200 kernels
+(`context_attention_fwd`, csrc/prefill.cu; the reference uses xformers for prompts without a prefix and a
+Triton kernel for prompts with one, xformers.py:291-318).
 """
 from dataclasses import dataclass
 from typing import Any, Dict, List, Literal, Optional, Tuple, Type
@@ -57,17 +57,50 @@ class B200PagedAttentionMetadata(AttentionMetadata, PagedAttentionMetadata):
     context_lens_tensor: Optional[torch.Tensor] = None
     use_cuda_graph: bool = False
 
+    _cached_prefill_metadata: Optional["B200PagedAttentionMetadata"] = None
+    _cached_decode_metadata: Optional["B200PagedAttentionMetadata"] = None
+
+    def _view(self, prefill: bool) -> "B200PagedAttentionMetadata":
+        """The prefill rows come first, then the decode rows (xformers.py:120-177): slice every per-sequence and
+        per-token field accordingly."""
+        npf, npt = self.num_prefills, self.num_prefill_tokens
+        seqs = slice(0, npf) if prefill else slice(npf, None)
+        toks = slice(0, npt) if prefill else slice(npt, None)
+        cut = lambda t, sl: None if t is None else t[sl]  # noqa: E731
+        return B200PagedAttentionMetadata(
+            num_prefills=npf if prefill else 0,
+            num_prefill_tokens=npt if prefill else 0,
+            num_decode_tokens=0 if prefill else self.num_decode_tokens,
+            slot_mapping=cut(self.slot_mapping, toks),
+            seq_lens=cut(self.seq_lens, seqs) if prefill else None,
+            seq_lens_tensor=cut(self.seq_lens_tensor, seqs),
+            max_query_len=self.max_query_len if prefill else None,
+            max_prefill_seq_len=self.max_prefill_seq_len if prefill else 0,
+            max_decode_seq_len=0 if prefill else self.max_decode_seq_len,
+            query_start_loc=cut(self.query_start_loc, slice(0, npf + 1)) if prefill else None,
+            seq_start_loc=None,
+            context_lens_tensor=cut(self.context_lens_tensor, seqs) if prefill else None,
+            block_tables=cut(self.block_tables, seqs),
+            use_cuda_graph=False if prefill else self.use_cuda_graph,
+        )
+
     @property
     def prefill_metadata(self) -> Optional["B200PagedAttentionMetadata"]:
         if self.num_prefills == 0:
             return None
-        return self  # prefill math is outside this path; callers only need the counts
+        if self._cached_prefill_metadata is None:
+            self._cached_prefill_metadata = self._view(prefill=True)
+        return self._cached_prefill_metadata
 
     @property
     def decode_metadata(self) -> Optional["B200PagedAttentionMetadata"]:
         if self.num_decode_tokens == 0:
             return None
-        return self
+        if self.num_prefills == 0:
+            return self
+        if self._cached_decode_metadata is None:
+            self._cached_decode_metadata = self._view(prefill=False)
+        return self._cached_decode_metadata
 
 
 class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
@@ -132,10 +165,16 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
         output = torch.empty_like(query)
         decode_query = query[num_prefill_tokens:]
 
+        if self.alibi_slopes is not None and self.alibi_slopes.device != query.device:
+            self.alibi_slopes = self.alibi_slopes.to(query.device)
+
+        if prefill_meta := attn_metadata.prefill_metadata:
+            output[:num_prefill_tokens] = self._forward_prefill(
+                query[:num_prefill_tokens], key[:num_prefill_tokens], value[:num_prefill_tokens],
+                key_cache, value_cache, prefill_meta)
+
         if decode_meta := attn_metadata.decode_metadata:
             assert kv_cache is not None, "decode needs the paged KV cache"
-            if self.alibi_slopes is not None and self.alibi_slopes.device != query.device:
-                self.alibi_slopes = self.alibi_slopes.to(query.device)
             bs = self.blocksparse_params
             output[num_prefill_tokens:] = PagedAttention.forward_decode(
                 decode_query, key_cache, value_cache, decode_meta.block_tables,
@@ -147,3 +186,23 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
                 blocksparse_block_size=bs.get("block_size", 64),
                 blocksparse_head_sliding_step=bs.get("head_sliding_step", 0))
         return output.view(-1, self.num_heads * self.head_size)
+
+    def _forward_prefill(self, query, key, value, key_cache, value_cache, meta) -> torch.Tensor:
+        """Prompt run (xformers.py:291-318).  With a cached prefix the reference calls
+        PagedAttention.forward_prefix; without one (no cache yet, or empty block tables) it runs plain causal
+        attention through xformers — here that is the same kernel with every context length 0."""
+        assert self.kv_cache_dtype == "auto", \
+            "prefix-prefill over an fp8 KV cache is unsupported (as in the reference, xformers.py:301-304)"
+        no_prefix = key_cache is None or meta.block_tables is None or meta.block_tables.numel() == 0
+        if no_prefix:
+            dev, nseq = query.device, meta.num_prefills
+            key_cache = torch.empty(1, self.num_kv_heads, self.head_size // 8, 8, 8, dtype=query.dtype, device=dev)
+            value_cache = torch.empty(1, self.num_kv_heads, self.head_size, 8, dtype=query.dtype, device=dev)
+            block_tables = torch.zeros(nseq, 1, dtype=torch.int32, device=dev)
+            context_lens = torch.zeros(nseq, dtype=torch.int32, device=dev)
+            seq_lens = meta.query_start_loc[1:nseq + 1] - meta.query_start_loc[:nseq]
+        else:
+            block_tables, context_lens, seq_lens = meta.block_tables, meta.context_lens_tensor, meta.seq_lens_tensor
+        return PagedAttention.forward_prefix(query, key, value, key_cache, value_cache, block_tables,
+                                             meta.query_start_loc, seq_lens, context_lens, meta.max_query_len,
+                                             self.alibi_slopes, self.sliding_window)

@@ -5,7 +5,7 @@ Same method names, arguments, KV-cache shape `(2, num_blocks, block_size*num_kv_
 K view `[nb, H, D/x, B, x]` / V view `[nb, H, D, B]`, V1/V2 selection rule and scratch shapes, so the
 reference's backends (xformers.py:269-335, hip.py:166-319, blocksparse_attn.py:357-390,
 torch_sdpa.py:162-216) and cache engine (cache_engine.py:89-100) can call it unchanged.
-`forward_prefix` (Triton prefix-prefill, third-party) is outside this path.
+`forward_prefix` runs the sm_100a prefix-prefill kernel (csrc/prefill.cu) instead of the reference's Triton one.
 """
 from dataclasses import dataclass
 from typing import List, Optional, Tuple
@@ -109,10 +109,40 @@ class PagedAttention:
         return output
 
     @staticmethod
-    def forward_prefix(*args, **kwargs) -> torch.Tensor:
-        raise NotImplementedError(
-            "forward_prefix (Triton context_attention_fwd, vllm/attention/ops/prefix_prefill.py) is "
-            "outside the paged-attention decode hot path; see SURVEY.md §8(f) rank 1.")
+    def forward_prefix(
+        query: torch.Tensor,
+        key: torch.Tensor,
+        value: torch.Tensor,
+        key_cache: torch.Tensor,
+        value_cache: torch.Tensor,
+        block_tables: torch.Tensor,
+        query_start_loc: torch.Tensor,
+        seq_lens_tensor: torch.Tensor,
+        context_lens: torch.Tensor,
+        max_query_len: int,
+        alibi_slopes: Optional[torch.Tensor],
+        sliding_window: Optional[int],
+    ) -> torch.Tensor:
+        """paged_attn.py:185-216: prefill of new tokens against the cached prefix + themselves."""
+        output = torch.empty_like(query)
+        # same call as vllm_legacy_b200.attention.ops.prefix_prefill.context_attention_fwd
+        ops.context_attention_fwd(
+            query,
+            key,
+            value,
+            output,
+            key_cache,
+            value_cache,
+            block_tables,
+            # query_start_loc is (batch_size + 1,)
+            query_start_loc[:-1],
+            seq_lens_tensor,
+            context_lens,
+            max_query_len,
+            alibi_slopes,
+            sliding_window,
+        )
+        return output
 
     @staticmethod
     def swap_blocks(src_kv_cache: torch.Tensor, dst_kv_cache: torch.Tensor,

@@ -1,0 +1,479 @@
+// context_attention_fwd for B200 (sm_100a): prefill attention of new tokens over (cached prefix in the
+// paged KV cache) + (the new tokens themselves, causal).  C-ABI entry b200pa_context_attention_fwd.
+//
+// Replaces the reference's Triton kernels `_fwd_kernel` / `_fwd_kernel_alibi` and their host wrapper
+// `context_attention_fwd` (vllm/attention/ops/prefix_prefill.py:10-245, 442-681, 684-817), reached through
+// PagedAttention.forward_prefix (vllm/attention/ops/paged_attn.py:185-216).
+//
+// Design (not the reference's):
+//   * one CTA = 64 query rows of one (sequence, query head); 4 warps x 16 rows; grid x = head so the
+//     CTAs that share a KV head (GQA group) are adjacent in launch order and hit the same K/V tiles in L2;
+//     heavy (late, long-causal) row tiles are scheduled first;
+//   * K/V tiles of BN tokens are staged by 16-byte cp.async into a double-buffered shared-memory ring and
+//     RE-LAID-OUT on the way: the paged K chunk [D/8][B][8] becomes token-major rows, the paged V chunk
+//     [D][B] becomes d-major rows, both with a 16-byte pad per row so every ldmatrix phase touches 8
+//     distinct bank groups.  The copy is block-size agnostic (any power of two >= 8);
+//   * QK^T and PV run on tensor cores (mma.sync.m16n8k16, fp32 accumulate); the S accumulator fragments
+//     are re-used in registers as the A operand of PV (no shared-memory round trip); V fragments come from
+//     ldmatrix (cached prefix, d-major) or ldmatrix.trans (new tokens, token-major);
+//   * online softmax in the log2 domain, finite -1e30 sentinel instead of -inf/-10000 (a fully masked
+//     tile contributes exactly 0 once a real logit is seen; every stored row sees its own diagonal);
+//   * KV tiles that the sliding window masks for all 64 rows are skipped, not computed and discarded.
+#include <algorithm>
+#include <type_traits>
+
+#include "attention_common.cuh"
+
+namespace b200pa {
+
+struct PrefillParams {
+  void* out;
+  const void* q;
+  const void* k;
+  const void* v;
+  const void* k_cache;
+  const void* v_cache;
+  const int* block_tables;
+  const int* start_loc;
+  const int* seq_lens;
+  const int* ctx_lens;
+  const float* alibi_slopes;
+  int64_t q_stride_t, q_stride_h, k_stride_t, k_stride_h, v_stride_t, v_stride_h, o_stride_t, o_stride_h;
+  int64_t kc_block_stride, kc_head_stride, vc_block_stride, vc_head_stride;  // elements
+  int64_t block_table_stride;
+  int num_heads, num_kv_heads, head_size, block_shift, sliding_window;
+  float scale_log2;  // scale * log2(e)
+};
+
+namespace prefill {
+
+constexpr int kThreads = 128;
+constexpr int kBM = 64;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+// 16-byte async copy global -> shared; src_bytes == 0 zero-fills the destination.
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+               : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+               : "r"(addr));
+}
+template <typename T>
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  if constexpr (std::is_same<T, __half>::value) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  } else {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  }
+}
+template <typename T>
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  if constexpr (std::is_same<T, __half>::value) {
+    __half2 h = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+  } else {
+    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+}
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int DP, int BN>
+struct Geometry {
+  static constexpr int KPITCH = (DP + 8) * 2;  // bytes per token-major row (K, new V)
+  static constexpr int VPITCH = (BN + 8) * 2;  // bytes per d-major row (cached V)
+  static constexpr int KBYTES = BN * KPITCH;
+  static constexpr int VBYTES = (BN * KPITCH > DP * VPITCH) ? BN * KPITCH : DP * VPITCH;
+  static constexpr int STAGE = KBYTES + VBYTES;
+  static constexpr int SMEM = 2 * STAGE;
+};
+
+// T: half | bf16 (query, new k/v, 16-bit cache, output).  DP: head size padded to a multiple of 16
+// (columns >= head_size are zero-filled).  BN: KV tokens per tile.
+template <typename T, int DP, int BN>
+__global__ void __launch_bounds__(kThreads, (DP <= 128) ? 3 : 1) context_attention_kernel(const __grid_constant__ PrefillParams p) {
+  using G = Geometry<DP, BN>;
+  constexpr int KS = DP / 16;  // k-steps of QK^T
+  constexpr int NT = BN / 8;   // 8-token n-tiles of S
+  constexpr int ND = DP / 8;   // 8-column n-tiles of O
+  constexpr int KK = BN / 16;  // k-steps of PV
+  constexpr int DG = DP / 8;   // 16-byte d-groups per token row
+  static_assert(DP % 16 == 0 && BN % 16 == 0 && kThreads % BN == 0, "tile geometry");
+
+  extern __shared__ __align__(128) uint8_t smem[];
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int gid = lane >> 2, tig = lane & 3;
+  const int mi = lane >> 3, mj = lane & 7;
+
+  const int head = blockIdx.x;
+  const int mt = gridDim.y - 1 - blockIdx.y;  // heavy row tiles first
+  const int seq = blockIdx.z;
+  const int ctx_len = p.ctx_lens[seq];
+  const int q_len = p.seq_lens[seq] - ctx_len;
+  const int m0 = mt * kBM;
+  if (m0 >= q_len) return;
+  const int64_t tok0 = p.start_loc[seq];
+  const int kv_head = head / (p.num_heads / p.num_kv_heads);
+  const int D = p.head_size;
+  const int W = p.alibi_slopes ? 0 : p.sliding_window;  // prefix_prefill.py:717-760: the ALiBi kernel has no window
+  const int bshift = p.block_shift;
+  const int B = 1 << bshift;
+
+  // ---- tile ranges ---------------------------------------------------------------------------------
+  // cached-prefix tiles [c_first, c_end), then new-token tiles [j_first, j_end) (causal upper bound)
+  int c_first = 0, j_first = 0;
+  if (W > 0) {
+    c_first = max(0, ctx_len + m0 - W + 1) / BN;  // keys below ctx_len + m0 - W + 1 are masked for every row
+    j_first = max(0, m0 - W + 1) / BN;
+  }
+  const int c_end = (ctx_len + BN - 1) / BN;
+  const int j_end = (min(q_len, m0 + kBM) + BN - 1) / BN;
+  const int n_ctx = max(0, c_end - c_first);
+  const int n_tiles = n_ctx + (j_end - j_first);
+
+  const T* kc = static_cast<const T*>(p.k_cache) + (int64_t)kv_head * p.kc_head_stride;
+  const T* vc = static_cast<const T*>(p.v_cache) + (int64_t)kv_head * p.vc_head_stride;
+  const T* kn = static_cast<const T*>(p.k) + tok0 * p.k_stride_t + (int64_t)kv_head * p.k_stride_h;
+  const T* vn = static_cast<const T*>(p.v) + tok0 * p.v_stride_t + (int64_t)kv_head * p.v_stride_h;
+  const int* table = p.block_tables + (int64_t)seq * p.block_table_stride;
+  const uint32_t smem_base = smem_u32(smem);
+
+  // ---- stage one KV tile (all threads) -----------------------------------------------------------
+  auto issue = [&](int it, int buf) {
+    const uint32_t kb = smem_base + buf * G::STAGE;
+    const uint32_t vb = kb + G::KBYTES;
+    if (it < n_ctx) {
+      const int t0 = (c_first + it) * BN;
+      {  // K: unit (d-group g, token t) of the paged chunk [D/8][B][8] -> row t, column group g
+        const int t = tid % BN;
+        const int kpos = t0 + t;
+        const bool tv = kpos < ctx_len;
+        const int64_t phys = tv ? table[kpos >> bshift] : 0;
+        const T* src = kc + phys * p.kc_block_stride + (kpos & (B - 1)) * 8;
+        const uint32_t dst = kb + t * G::KPITCH;
+#pragma unroll
+        for (int g = tid / BN; g < DG; g += kThreads / BN) {
+          const bool ok = tv && g * 8 < D;
+          cp_async16(dst + g * 16, ok ? (const void*)(src + (int64_t)g * B * 8) : (const void*)kc, ok ? 16 : 0);
+        }
+      }
+      {  // V: 8 consecutive tokens of one d row of the paged chunk [D][B] -> d-major row
+        const int rshift = min(bshift, (BN == 64 ? 6 : 5));  // tokens per contiguous run R = min(B, BN)
+        const int R = 1 << rshift;
+        const int upr_shift = rshift - 3;                 // 16-byte units per (d row, run)
+        const int units_per_run = DP << upr_shift;
+#pragma unroll 4
+        for (int u = tid; u < DP * BN / 8; u += kThreads) {
+          const int run = u / units_per_run;
+          const int rem = u - run * units_per_run;
+          const int d = rem >> upr_shift;
+          const int tt = run * R + ((rem & ((1 << upr_shift) - 1)) << 3);  // token inside the tile
+          const int kpos = t0 + tt;
+          const bool ok = kpos < ctx_len && d < D;
+          const int64_t phys = ok ? table[kpos >> bshift] : 0;
+          const T* src = vc + phys * p.vc_block_stride + (int64_t)d * B + (kpos & (B - 1));
+          cp_async16(vb + d * G::VPITCH + tt * 2, ok ? (const void*)src : (const void*)vc, ok ? 16 : 0);
+        }
+      }
+    } else {
+      const int t0 = (j_first + it - n_ctx) * BN;
+#pragma unroll 4
+      for (int u = tid; u < BN * DG; u += kThreads) {
+        const int r = u / DG, c = u - r * DG;
+        const int j = t0 + r;
+        const bool ok = j < q_len && c * 8 < D;
+        const uint32_t off = r * G::KPITCH + c * 16;
+        cp_async16(kb + off, ok ? (const void*)(kn + (int64_t)j * p.k_stride_t + c * 8) : (const void*)kn, ok ? 16 : 0);
+        cp_async16(vb + off, ok ? (const void*)(vn + (int64_t)j * p.v_stride_t + c * 8) : (const void*)vn, ok ? 16 : 0);
+      }
+    }
+    cp_async_commit();
+  };
+
+  issue(0, 0);
+
+  // ---- Q fragments: rows m0 + 16 warp + {gid, gid + 8} ------------------------------------------
+  const int mrow0 = m0 + warp * 16 + gid;
+  uint32_t qa[KS][4];
+  {
+    const T* qb = static_cast<const T*>(p.q) + (int64_t)head * p.q_stride_h;
+    const T* q0 = qb + (tok0 + mrow0) * p.q_stride_t;
+    const T* q1 = qb + (tok0 + mrow0 + 8) * p.q_stride_t;
+    const bool v0 = mrow0 < q_len, v1 = mrow0 + 8 < q_len;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      const int d0 = 16 * ks + 2 * tig, d1 = d0 + 8;
+      qa[ks][0] = (v0 && d0 < D) ? *reinterpret_cast<const uint32_t*>(q0 + d0) : 0u;
+      qa[ks][1] = (v1 && d0 < D) ? *reinterpret_cast<const uint32_t*>(q1 + d0) : 0u;
+      qa[ks][2] = (v0 && d1 < D) ? *reinterpret_cast<const uint32_t*>(q0 + d1) : 0u;
+      qa[ks][3] = (v1 && d1 < D) ? *reinterpret_cast<const uint32_t*>(q1 + d1) : 0u;
+    }
+  }
+  const float slope_l2 = p.alibi_slopes ? p.alibi_slopes[head] * kLog2e : 0.f;
+  const bool has_alibi = p.alibi_slopes != nullptr;
+
+  float m_run[2] = {kNegBig, kNegBig}, l_run[2] = {0.f, 0.f};
+  float oacc[ND][4];
+#pragma unroll
+  for (int nd = 0; nd < ND; ++nd)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) oacc[nd][e] = 0.f;
+
+  // per-lane ldmatrix offsets
+  const uint32_t k_lane = ((mi >> 1) * 8 + mj) * G::KPITCH + (mi & 1) * 16;   // (n-tile pair, d half)
+  const uint32_t vc_lane = ((mi >> 1) * 8 + mj) * G::VPITCH + (mi & 1) * 16;  // d-major: (d tile pair, token half)
+  const uint32_t vn_lane = ((mi & 1) * 8 + mj) * G::KPITCH + (mi >> 1) * 16;  // token-major, .trans
+
+  for (int it = 0; it < n_tiles; ++it) {
+    const int buf = it & 1;
+    if (it + 1 < n_tiles) {
+      issue(it + 1, buf ^ 1);
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads();
+    const uint32_t kb = smem_base + buf * G::STAGE;
+    const uint32_t vb = kb + G::KBYTES;
+    const bool is_ctx = it < n_ctx;
+    const int t0 = is_ctx ? (c_first + it) * BN : (j_first + it - n_ctx) * BN;
+
+    if (is_ctx && t0 + BN > ctx_len) {
+      // last prefix tile: zero the V columns of tokens >= ctx_len (stale cache bits there could be NaN,
+      // and 0 * NaN would poison the row; the reference masks the load, prefix_prefill.py:163-167)
+      const int nvalid = ctx_len - t0, cnt = BN - nvalid;
+      T* vrow = reinterpret_cast<T*>(smem + buf * G::STAGE + G::KBYTES);
+      for (int idx = tid; idx < DP * cnt; idx += kThreads) {
+        const int d = idx / cnt, c = nvalid + (idx - d * cnt);
+        vrow[d * (G::VPITCH / 2) + c] = from_float<T>(0.f);
+      }
+      __syncthreads();
+    }
+
+    // ================= S = Q K^T =================
+    float sacc[NT][4];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) sacc[nt][e] = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+      for (int np = 0; np < NT / 2; ++np) {
+        uint32_t r0, r1, r2, r3;
+        ldsm_x4(kb + np * 16 * G::KPITCH + ks * 32 + k_lane, r0, r1, r2, r3);
+        mma16816<T>(sacc[2 * np], qa[ks], r0, r1);
+        mma16816<T>(sacc[2 * np + 1], qa[ks], r2, r3);
+      }
+    }
+
+    // ================= mask + online softmax =================
+    // this lane: rows h = 0 (mrow0), 1 (mrow0 + 8); columns 8 nt + 2 tig + e
+    uint32_t pa[KK][4];
+    float alpha[2];
+    {
+      // key position relative to the query position: rel = kpos_abs - qpos_abs (<= 0 when visible)
+      const int base_rel = is_ctx ? (t0 - ctx_len) : t0;  // + col - m
+      const int col_limit = is_ctx ? (ctx_len - t0) : BN;  // columns >= col_limit are past the cached prefix
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int m = mrow0 + 8 * h;
+        float mx = kNegBig;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int col = 8 * nt + 2 * tig + e;
+            const int rel = base_rel + col - m;
+            float z = sacc[nt][2 * h + e] * p.scale_log2;
+            if (has_alibi) z = fmaf(slope_l2, (float)rel, z);
+            const bool vis = col < col_limit && rel <= 0 && (W <= 0 || -rel < W);
+            z = vis ? z : kNegBig;
+            sacc[nt][2 * h + e] = z;
+            mx = fmaxf(mx, z);
+          }
+        }
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        const float m_new = fmaxf(m_run[h], mx);
+        alpha[h] = ex2(m_run[h] - m_new);
+        m_run[h] = m_new;
+        float sum = 0.f;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+          const float p0 = ex2(sacc[nt][2 * h] - m_new), p1 = ex2(sacc[nt][2 * h + 1] - m_new);
+          sum += p0 + p1;
+          // A fragment of PV: k-step nt/2; a0/a1 (rows gid/gid+8, k 2tig..) from even nt, a2/a3 from odd nt
+          pa[nt >> 1][(nt & 1) * 2 + h] = pack2<T>(p0, p1);
+        }
+        l_run[h] = l_run[h] * alpha[h] + sum;  // per-lane partial; quad-reduced at the end
+      }
+    }
+    if (__any_sync(0xffffffffu, alpha[0] != 1.f || alpha[1] != 1.f)) {
+#pragma unroll
+      for (int nd = 0; nd < ND; ++nd) {
+        oacc[nd][0] *= alpha[0];
+        oacc[nd][1] *= alpha[0];
+        oacc[nd][2] *= alpha[1];
+        oacc[nd][3] *= alpha[1];
+      }
+    }
+
+    // ================= O += P V =================
+    if (is_ctx) {
+#pragma unroll
+      for (int kk = 0; kk < KK; ++kk)
+#pragma unroll
+        for (int dp = 0; dp < ND / 2; ++dp) {
+          uint32_t r0, r1, r2, r3;
+          ldsm_x4(vb + dp * 16 * G::VPITCH + kk * 32 + vc_lane, r0, r1, r2, r3);
+          mma16816<T>(oacc[2 * dp], pa[kk], r0, r1);
+          mma16816<T>(oacc[2 * dp + 1], pa[kk], r2, r3);
+        }
+    } else {
+#pragma unroll
+      for (int kk = 0; kk < KK; ++kk)
+#pragma unroll
+        for (int dp = 0; dp < ND / 2; ++dp) {
+          uint32_t r0, r1, r2, r3;
+          ldsm_x4_t(vb + kk * 16 * G::KPITCH + dp * 32 + vn_lane, r0, r1, r2, r3);
+          mma16816<T>(oacc[2 * dp], pa[kk], r0, r1);
+          mma16816<T>(oacc[2 * dp + 1], pa[kk], r2, r3);
+        }
+    }
+    __syncthreads();  // everyone is done with `buf` before the next iteration refills it
+  }
+
+  // ---- epilogue ---------------------------------------------------------------------------------------
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    float l = l_run[h];
+    l += __shfl_xor_sync(0xffffffffu, l, 1);
+    l += __shfl_xor_sync(0xffffffffu, l, 2);
+    const int m = mrow0 + 8 * h;
+    if (m >= q_len) continue;
+    const float inv = 1.f / l;  // l > 0: every stored row sees at least its own key
+    T* orow = static_cast<T*>(p.out) + (tok0 + m) * p.o_stride_t + (int64_t)head * p.o_stride_h;
+#pragma unroll
+    for (int nd = 0; nd < ND; ++nd) {
+      const int d = 8 * nd + 2 * tig;
+      if (d < D) *reinterpret_cast<uint32_t*>(orow + d) = pack2<T>(oacc[nd][2 * h] * inv, oacc[nd][2 * h + 1] * inv);
+    }
+  }
+}
+
+template <typename T, int DP, int BN>
+static int launch(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
+  using G = Geometry<DP, BN>;
+  auto kernel = context_attention_kernel<T, DP, BN>;
+  static bool configured[64] = {false};
+  int dev = 0;
+  B200PA_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    B200PA_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM));
+    if (dev >= 0 && dev < 64) configured[dev] = true;
+  }
+  dim3 grid(kp.num_heads, (max_query_len + kBM - 1) / kBM, batch);
+  kernel<<<grid, kThreads, G::SMEM, stream>>>(kp);
+  B200PA_CUDA_CHECK(cudaGetLastError());
+  return B200PA_OK;
+}
+
+template <typename T>
+static int launch_t(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
+  const int d = kp.head_size;
+  if (d <= 32) return launch<T, 32, 64>(kp, batch, max_query_len, stream);
+  if (d <= 64) return launch<T, 64, 64>(kp, batch, max_query_len, stream);
+  if (d <= 96) return launch<T, 96, 64>(kp, batch, max_query_len, stream);
+  if (d <= 128) return launch<T, 128, 64>(kp, batch, max_query_len, stream);
+  if (d <= 192) return launch<T, 192, 32>(kp, batch, max_query_len, stream);
+  return launch<T, 256, 32>(kp, batch, max_query_len, stream);
+}
+
+}  // namespace prefill
+}  // namespace b200pa
+
+extern "C" int b200pa_context_attention_fwd(const b200pa_prefill_params_t* a, b200pa_stream_t stream) {
+  using namespace b200pa;
+  if (!a) return B200PA_ERR_INVALID_ARG;
+  if (a->dtype != B200PA_F16 && a->dtype != B200PA_BF16) return B200PA_ERR_INPUT_DTYPE;
+  if (a->kv_dtype != B200PA_KV_AUTO) return B200PA_ERR_KV_DTYPE;
+  if (a->head_size <= 0 || a->head_size > 256 || a->head_size % 8 != 0) return B200PA_ERR_HEAD_SIZE;
+  int bshift = 0;
+  while ((1 << bshift) < a->block_size) ++bshift;
+  if (a->block_size < 8 || (1 << bshift) != a->block_size) return B200PA_ERR_BLOCK_SIZE;
+  if (a->batch < 0 || a->max_query_len < 0 || a->num_heads <= 0 || a->num_kv_heads <= 0 ||
+      a->num_heads % a->num_kv_heads != 0)
+    return B200PA_ERR_INVALID_ARG;
+  if (a->batch == 0 || a->max_query_len == 0) return B200PA_OK;
+  if (!a->out || !a->query || !a->key || !a->value || !a->key_cache || !a->value_cache || !a->block_tables ||
+      !a->start_loc || !a->seq_lens || !a->ctx_lens)
+    return B200PA_ERR_INVALID_ARG;
+  auto mis = [](const void* ptr, int n) { return reinterpret_cast<uintptr_t>(ptr) % n != 0; };
+  // 16-byte cp.async rows for k / v / caches, 32-bit accesses for q / out
+  if (mis(a->key, 16) || mis(a->value, 16) || mis(a->key_cache, 16) || mis(a->value_cache, 16) || mis(a->query, 4) ||
+      mis(a->out, 4) || a->k_stride_t % 8 || a->k_stride_h % 8 || a->v_stride_t % 8 || a->v_stride_h % 8 ||
+      a->kc_block_stride % 8 || a->kc_head_stride % 8 || a->vc_block_stride % 8 || a->vc_head_stride % 8 ||
+      a->q_stride_t % 2 || a->q_stride_h % 2 || a->o_stride_t % 2 || a->o_stride_h % 2)
+    return B200PA_ERR_INVALID_ARG;
+
+  PrefillParams kp{};
+  kp.out = a->out;
+  kp.q = a->query;
+  kp.k = a->key;
+  kp.v = a->value;
+  kp.k_cache = a->key_cache;
+  kp.v_cache = a->value_cache;
+  kp.block_tables = a->block_tables;
+  kp.start_loc = a->start_loc;
+  kp.seq_lens = a->seq_lens;
+  kp.ctx_lens = a->ctx_lens;
+  kp.alibi_slopes = a->alibi_slopes;
+  kp.q_stride_t = a->q_stride_t;
+  kp.q_stride_h = a->q_stride_h;
+  kp.k_stride_t = a->k_stride_t;
+  kp.k_stride_h = a->k_stride_h;
+  kp.v_stride_t = a->v_stride_t;
+  kp.v_stride_h = a->v_stride_h;
+  kp.o_stride_t = a->o_stride_t;
+  kp.o_stride_h = a->o_stride_h;
+  kp.kc_block_stride = a->kc_block_stride;
+  kp.kc_head_stride = a->kc_head_stride;
+  kp.vc_block_stride = a->vc_block_stride;
+  kp.vc_head_stride = a->vc_head_stride;
+  kp.block_table_stride = a->block_table_stride;
+  kp.num_heads = a->num_heads;
+  kp.num_kv_heads = a->num_kv_heads;
+  kp.head_size = a->head_size;
+  kp.block_shift = bshift;
+  kp.sliding_window = a->sliding_window > 0 ? a->sliding_window : 0;
+  kp.scale_log2 = a->scale * kLog2e;
+  if (a->dtype == B200PA_F16) return prefill::launch_t<__half>(kp, a->batch, a->max_query_len, stream);
+  return prefill::launch_t<__nv_bfloat16>(kp, a->batch, a->max_query_len, stream);
+}

@@ -8,6 +8,7 @@
 #include <c10/cuda/CUDAGuard.h>
 #include <torch/extension.h>
 
+#include <cmath>
 #include <string>
 #include <vector>
 
@@ -378,6 +379,79 @@ int get_max_shared_memory_per_block_device_attribute(int device_id) {
   return v;
 }
 
+// vllm/attention/ops/prefix_prefill.py:684-696 (context_attention_fwd), same argument order.  The
+// index tensors may be int32 (vLLM's metadata) or int64 (the reference's kernel test); int64 ones are
+// narrowed here.  scale = 1/sqrt(head_size) as the reference's wrapper fixes it (:706).
+void context_attention_fwd(torch::Tensor& q, torch::Tensor& k, torch::Tensor& v, torch::Tensor& o,
+                           torch::Tensor& k_cache, torch::Tensor& v_cache, torch::Tensor& b_loc,
+                           torch::Tensor& b_start_loc, torch::Tensor& b_seq_len, torch::Tensor& b_ctx_len,
+                           int max_input_len, const c10::optional<torch::Tensor>& alibi_slopes,
+                           const c10::optional<int64_t>& sliding_window) {
+  TORCH_CHECK(q.is_cuda() && k.is_cuda() && v.is_cuda() && o.is_cuda() && k_cache.is_cuda() && v_cache.is_cuda() &&
+                  b_loc.is_cuda() && b_start_loc.is_cuda() && b_seq_len.is_cuda() && b_ctx_len.is_cuda(),
+              "b200pa context_attention_fwd: tensors must be on a CUDA device (there is no CPU path)");
+  TORCH_CHECK(q.dim() == 3 && k.dim() == 3 && v.dim() == 3 && o.dim() == 3, "q, k, v, o must be [tokens, heads, head_size]");
+  TORCH_CHECK(q.size(2) == k.size(2) && k.size(2) == v.size(2), "q, k, v head sizes differ");  // :702-703
+  TORCH_CHECK(q.stride(2) == 1 && k.stride(2) == 1 && v.stride(2) == 1 && o.stride(2) == 1,
+              "q, k, v, o must be contiguous in head_size");
+  TORCH_CHECK(k.scalar_type() == q.scalar_type() && v.scalar_type() == q.scalar_type() &&
+                  o.scalar_type() == q.scalar_type(), "q, k, v, o dtypes differ");
+  TORCH_CHECK(k_cache.dim() == 5 && v_cache.dim() == 4, "k_cache must be [nb, H, D/x, B, x], v_cache [nb, H, D, B]");
+  TORCH_CHECK(k_cache.stride(4) == 1 && k_cache.stride(3) == k_cache.size(4) &&
+                  k_cache.stride(2) == k_cache.size(3) * k_cache.size(4) && v_cache.stride(3) == 1 &&
+                  v_cache.stride(2) == v_cache.size(3),
+              "cache blocks must be contiguous per (block, head)");
+  TORCH_CHECK(b_loc.dim() == 2, "b_loc must be [batch, max_blocks]");
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(q));
+  auto as_i32 = [](torch::Tensor& t) {
+    TORCH_CHECK(t.scalar_type() == at::ScalarType::Int || t.scalar_type() == at::ScalarType::Long,
+                "index tensors must be int32 or int64");
+    torch::Tensor r = t.scalar_type() == at::ScalarType::Int ? t : t.to(at::ScalarType::Int);
+    return r.stride(-1) == 1 ? r : r.contiguous();
+  };
+  torch::Tensor loc = as_i32(b_loc), start = as_i32(b_start_loc), seql = as_i32(b_seq_len), ctxl = as_i32(b_ctx_len);
+  b200pa_prefill_params_t p{};
+  p.out = o.data_ptr();
+  p.query = q.data_ptr();
+  p.key = k.data_ptr();
+  p.value = v.data_ptr();
+  p.key_cache = k_cache.data_ptr();
+  p.value_cache = v_cache.data_ptr();
+  p.block_tables = loc.data_ptr<int>();
+  p.start_loc = start.data_ptr<int>();
+  p.seq_lens = seql.data_ptr<int>();
+  p.ctx_lens = ctxl.data_ptr<int>();
+  if (alibi_slopes.has_value()) {
+    TORCH_CHECK(alibi_slopes->scalar_type() == at::ScalarType::Float && alibi_slopes->is_cuda() &&
+                    alibi_slopes->is_contiguous(), "alibi_slopes must be a contiguous float32 CUDA tensor");
+    p.alibi_slopes = alibi_slopes->data_ptr<float>();
+  }
+  p.q_stride_t = q.stride(0); p.q_stride_h = q.stride(1);
+  p.k_stride_t = k.stride(0); p.k_stride_h = k.stride(1);
+  p.v_stride_t = v.stride(0); p.v_stride_h = v.stride(1);
+  p.o_stride_t = o.stride(0); p.o_stride_h = o.stride(1);
+  p.kc_block_stride = k_cache.stride(0); p.kc_head_stride = k_cache.stride(1);
+  p.vc_block_stride = v_cache.stride(0); p.vc_head_stride = v_cache.stride(1);
+  p.block_table_stride = loc.stride(0);
+  p.batch = seql.size(0);
+  p.max_query_len = max_input_len;
+  p.num_heads = q.size(1);
+  p.num_kv_heads = k.size(1);
+  p.head_size = q.size(2);
+  p.block_size = v_cache.size(3);
+  p.sliding_window = sliding_window.has_value() ? static_cast<int>(*sliding_window) : 0;
+  p.dtype = scalar_dtype(q);
+  const int cdt = scalar_dtype(k_cache);
+  TORCH_CHECK(cdt == p.dtype && k_cache.size(4) * k_cache.element_size() == 16 && v_cache.scalar_type() == k_cache.scalar_type(),
+              "context_attention_fwd: the paged cache must have the query dtype (kv_cache_dtype=\"auto\", x = 8)");
+  p.kv_dtype = B200PA_KV_AUTO;
+  p.scale = 1.0f / std::sqrt(static_cast<float>(p.head_size));
+  const int rc = b200pa_context_attention_fwd(&p, current_stream());
+  if (rc == B200PA_ERR_HEAD_SIZE) TORCH_CHECK(false, "Unsupported head size: ", p.head_size);
+  if (rc == B200PA_ERR_BLOCK_SIZE) TORCH_CHECK(false, "Unsupported block size: ", p.block_size);
+  check_status(rc, nullptr, q, "auto");
+}
+
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
@@ -387,6 +461,12 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           "Compute the attention between an input query and the cached keys/values using PagedAttention.");
   ops.def("paged_attention_v2", &paged_attention_v2, "PagedAttention V2.");
   // csrc/pybind.cpp:33-38
+  ops.def("context_attention_fwd", &context_attention_fwd,
+          "Prefill attention of new tokens over the cached prefix (paged cache) + themselves (causal)",
+          pybind11::arg("q"), pybind11::arg("k"), pybind11::arg("v"), pybind11::arg("o"), pybind11::arg("k_cache"),
+          pybind11::arg("v_cache"), pybind11::arg("b_loc"), pybind11::arg("b_start_loc"), pybind11::arg("b_seq_len"),
+          pybind11::arg("b_ctx_len"), pybind11::arg("max_input_len"), pybind11::arg("alibi_slopes") = pybind11::none(),
+          pybind11::arg("sliding_window") = pybind11::none());
   ops.def("rotary_embedding", &rotary_embedding, "Apply GPT-NeoX or GPT-J style rotary embedding to query and key");
   ops.def("batched_rotary_embedding", &batched_rotary_embedding,
           "Apply GPT-NeoX or GPT-J style rotary embedding to query and key (batched cos/sin offsets)");
