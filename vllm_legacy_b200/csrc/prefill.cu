@@ -20,6 +20,7 @@
 //     tile contributes exactly 0 once a real logit is seen; every stored row sees its own diagonal);
 //   * KV tiles that the sliding window masks for all 64 rows are skipped, not computed and discarded.
 #include <algorithm>
+#include <cstdlib>
 #include <type_traits>
 
 #include "attention_common.cuh"
@@ -102,21 +103,26 @@ __device__ __forceinline__ float ex2(float x) {
   return y;
 }
 
-template <int DP, int BN>
+template <int DP, int BN, int MT>
 struct Geometry {
-  static constexpr int KPITCH = (DP + 8) * 2;  // bytes per token-major row (K, new V)
+  static constexpr int BM = 64 * MT;           // query rows per CTA (4 warps x MT m16 tiles)
+  static constexpr int KPITCH = (DP + 8) * 2;  // bytes per token-major row (Q, K, new V)
   static constexpr int VPITCH = (BN + 8) * 2;  // bytes per d-major row (cached V)
+  static constexpr int QBYTES = BM * KPITCH;
   static constexpr int KBYTES = BN * KPITCH;
   static constexpr int VBYTES = (BN * KPITCH > DP * VPITCH) ? BN * KPITCH : DP * VPITCH;
   static constexpr int STAGE = KBYTES + VBYTES;
-  static constexpr int SMEM = 2 * STAGE;
+  static constexpr int SMEM = QBYTES + 2 * STAGE;
 };
 
 // T: half | bf16 (query, new k/v, 16-bit cache, output).  DP: head size padded to a multiple of 16
-// (columns >= head_size are zero-filled).  BN: KV tokens per tile.
-template <typename T, int DP, int BN>
-__global__ void __launch_bounds__(kThreads, (DP <= 128) ? 3 : 1) context_attention_kernel(const __grid_constant__ PrefillParams p) {
-  using G = Geometry<DP, BN>;
+// (columns >= head_size are zero-filled).  BN: KV tokens per tile.  MT: m16 row tiles per warp — with
+// MT = 2 every K/V fragment read from shared memory feeds two MMAs and every staged tile serves 128 rows.
+template <typename T, int DP, int BN, int MT>
+__global__ void __launch_bounds__(kThreads, (DP <= 128 && MT == 1) ? 3 : (DP <= 128 ? 2 : 1))
+    context_attention_kernel(const __grid_constant__ PrefillParams p) {
+  using G = Geometry<DP, BN, MT>;
+  constexpr int BM = G::BM;
   constexpr int KS = DP / 16;  // k-steps of QK^T
   constexpr int NT = BN / 8;   // 8-token n-tiles of S
   constexpr int ND = DP / 8;   // 8-column n-tiles of O
@@ -132,11 +138,11 @@ __global__ void __launch_bounds__(kThreads, (DP <= 128) ? 3 : 1) context_attenti
   const int mi = lane >> 3, mj = lane & 7;
 
   const int head = blockIdx.x;
-  const int mt = gridDim.y - 1 - blockIdx.y;  // heavy row tiles first
+  const int mt_idx = gridDim.y - 1 - blockIdx.y;  // heavy row tiles first
   const int seq = blockIdx.z;
   const int ctx_len = p.ctx_lens[seq];
   const int q_len = p.seq_lens[seq] - ctx_len;
-  const int m0 = mt * kBM;
+  const int m0 = mt_idx * BM;
   if (m0 >= q_len) return;
   const int64_t tok0 = p.start_loc[seq];
   const int kv_head = head / (p.num_heads / p.num_kv_heads);
@@ -153,7 +159,7 @@ __global__ void __launch_bounds__(kThreads, (DP <= 128) ? 3 : 1) context_attenti
     j_first = max(0, m0 - W + 1) / BN;
   }
   const int c_end = (ctx_len + BN - 1) / BN;
-  const int j_end = (min(q_len, m0 + kBM) + BN - 1) / BN;
+  const int j_end = (min(q_len, m0 + BM) + BN - 1) / BN;
   const int n_ctx = max(0, c_end - c_first);
   const int n_tiles = n_ctx + (j_end - j_first);
 
@@ -162,11 +168,12 @@ __global__ void __launch_bounds__(kThreads, (DP <= 128) ? 3 : 1) context_attenti
   const T* kn = static_cast<const T*>(p.k) + tok0 * p.k_stride_t + (int64_t)kv_head * p.k_stride_h;
   const T* vn = static_cast<const T*>(p.v) + tok0 * p.v_stride_t + (int64_t)kv_head * p.v_stride_h;
   const int* table = p.block_tables + (int64_t)seq * p.block_table_stride;
-  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t q_smem = smem_u32(smem);
+  const uint32_t kv_smem = q_smem + G::QBYTES;
 
   // ---- stage one KV tile (all threads) -----------------------------------------------------------
   auto issue = [&](int it, int buf) {
-    const uint32_t kb = smem_base + buf * G::STAGE;
+    const uint32_t kb = kv_smem + buf * G::STAGE;
     const uint32_t vb = kb + G::KBYTES;
     if (it < n_ctx) {
       const int t0 = (c_first + it) * BN;
@@ -213,39 +220,50 @@ __global__ void __launch_bounds__(kThreads, (DP <= 128) ? 3 : 1) context_attenti
         cp_async16(vb + off, ok ? (const void*)(vn + (int64_t)j * p.v_stride_t + c * 8) : (const void*)vn, ok ? 16 : 0);
       }
     }
-    cp_async_commit();
   };
 
-  issue(0, 0);
-
-  // ---- Q fragments: rows m0 + 16 warp + {gid, gid + 8} ------------------------------------------
-  const int mrow0 = m0 + warp * 16 + gid;
-  uint32_t qa[KS][4];
+  // ---- Q tile -> shared (rows >= q_len and columns >= head_size zero-filled), with the first KV tile ----
   {
-    const T* qb = static_cast<const T*>(p.q) + (int64_t)head * p.q_stride_h;
-    const T* q0 = qb + (tok0 + mrow0) * p.q_stride_t;
-    const T* q1 = qb + (tok0 + mrow0 + 8) * p.q_stride_t;
-    const bool v0 = mrow0 < q_len, v1 = mrow0 + 8 < q_len;
-#pragma unroll
-    for (int ks = 0; ks < KS; ++ks) {
-      const int d0 = 16 * ks + 2 * tig, d1 = d0 + 8;
-      qa[ks][0] = (v0 && d0 < D) ? *reinterpret_cast<const uint32_t*>(q0 + d0) : 0u;
-      qa[ks][1] = (v1 && d0 < D) ? *reinterpret_cast<const uint32_t*>(q1 + d0) : 0u;
-      qa[ks][2] = (v0 && d1 < D) ? *reinterpret_cast<const uint32_t*>(q0 + d1) : 0u;
-      qa[ks][3] = (v1 && d1 < D) ? *reinterpret_cast<const uint32_t*>(q1 + d1) : 0u;
+    const T* qb = static_cast<const T*>(p.q) + tok0 * p.q_stride_t + (int64_t)head * p.q_stride_h;
+    const bool q16 = (reinterpret_cast<uintptr_t>(p.q) % 16 == 0) && (p.q_stride_t % 8 == 0) && (p.q_stride_h % 8 == 0);
+    if (q16) {
+#pragma unroll 4
+      for (int u = tid; u < BM * DG; u += kThreads) {
+        const int r = u / DG, c = u - r * DG;
+        const bool ok = m0 + r < q_len && c * 8 < D;
+        cp_async16(q_smem + r * G::KPITCH + c * 16, ok ? (const void*)(qb + (int64_t)(m0 + r) * p.q_stride_t + c * 8) : (const void*)qb,
+                   ok ? 16 : 0);
+      }
+    } else {  // 4-byte aligned query rows: plain 32-bit copies
+      for (int u = tid; u < BM * (DP / 2); u += kThreads) {
+        const int r = u / (DP / 2), c = u - r * (DP / 2);
+        const bool ok = m0 + r < q_len && c * 2 < D;
+        const uint32_t w = ok ? *reinterpret_cast<const uint32_t*>(qb + (int64_t)(m0 + r) * p.q_stride_t + c * 2) : 0u;
+        *reinterpret_cast<uint32_t*>(smem + r * G::KPITCH + c * 4) = w;
+      }
     }
   }
+  issue(0, 0);
+  cp_async_commit();
+
   const float slope_l2 = p.alibi_slopes ? p.alibi_slopes[head] * kLog2e : 0.f;
   const bool has_alibi = p.alibi_slopes != nullptr;
+  const int wrow0 = m0 + warp * (16 * MT);  // first query row of this warp
 
-  float m_run[2] = {kNegBig, kNegBig}, l_run[2] = {0.f, 0.f};
-  float oacc[ND][4];
+  float m_run[MT][2], l_run[MT][2];
+  float oacc[MT][ND][4];
 #pragma unroll
-  for (int nd = 0; nd < ND; ++nd)
+  for (int i = 0; i < MT; ++i) {
+    m_run[i][0] = m_run[i][1] = kNegBig;
+    l_run[i][0] = l_run[i][1] = 0.f;
 #pragma unroll
-    for (int e = 0; e < 4; ++e) oacc[nd][e] = 0.f;
+    for (int nd = 0; nd < ND; ++nd)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) oacc[i][nd][e] = 0.f;
+  }
 
   // per-lane ldmatrix offsets
+  const uint32_t q_lane = q_smem + (warp * (16 * MT) + (mi & 1) * 8 + mj) * G::KPITCH + (mi >> 1) * 16;  // A: (row half, k half)
   const uint32_t k_lane = ((mi >> 1) * 8 + mj) * G::KPITCH + (mi & 1) * 16;   // (n-tile pair, d half)
   const uint32_t vc_lane = ((mi >> 1) * 8 + mj) * G::VPITCH + (mi & 1) * 16;  // d-major: (d tile pair, token half)
   const uint32_t vn_lane = ((mi & 1) * 8 + mj) * G::KPITCH + (mi >> 1) * 16;  // token-major, .trans
@@ -254,12 +272,13 @@ __global__ void __launch_bounds__(kThreads, (DP <= 128) ? 3 : 1) context_attenti
     const int buf = it & 1;
     if (it + 1 < n_tiles) {
       issue(it + 1, buf ^ 1);
+      cp_async_commit();
       cp_async_wait<1>();
     } else {
       cp_async_wait<0>();
     }
     __syncthreads();
-    const uint32_t kb = smem_base + buf * G::STAGE;
+    const uint32_t kb = kv_smem + buf * G::STAGE;
     const uint32_t vb = kb + G::KBYTES;
     const bool is_ctx = it < n_ctx;
     const int t0 = is_ctx ? (c_first + it) * BN : (j_first + it - n_ctx) * BN;
@@ -268,7 +287,7 @@ __global__ void __launch_bounds__(kThreads, (DP <= 128) ? 3 : 1) context_attenti
       // last prefix tile: zero the V columns of tokens >= ctx_len (stale cache bits there could be NaN,
       // and 0 * NaN would poison the row; the reference masks the load, prefix_prefill.py:163-167)
       const int nvalid = ctx_len - t0, cnt = BN - nvalid;
-      T* vrow = reinterpret_cast<T*>(smem + buf * G::STAGE + G::KBYTES);
+      T* vrow = reinterpret_cast<T*>(smem + G::QBYTES + buf * G::STAGE + G::KBYTES);
       for (int idx = tid; idx < DP * cnt; idx += kThreads) {
         const int d = idx / cnt, c = nvalid + (idx - d * cnt);
         vrow[d * (G::VPITCH / 2) + c] = from_float<T>(0.f);
@@ -277,72 +296,101 @@ __global__ void __launch_bounds__(kThreads, (DP <= 128) ? 3 : 1) context_attenti
     }
 
     // ================= S = Q K^T =================
-    float sacc[NT][4];
+    float sacc[MT][NT][4];
 #pragma unroll
-    for (int nt = 0; nt < NT; ++nt)
+    for (int i = 0; i < MT; ++i)
 #pragma unroll
-      for (int e = 0; e < 4; ++e) sacc[nt][e] = 0.f;
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) sacc[i][nt][e] = 0.f;
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks) {
+      uint32_t qa[MT][4];
+#pragma unroll
+      for (int i = 0; i < MT; ++i) ldsm_x4(q_lane + i * 16 * G::KPITCH + ks * 32, qa[i][0], qa[i][1], qa[i][2], qa[i][3]);
 #pragma unroll
       for (int np = 0; np < NT / 2; ++np) {
         uint32_t r0, r1, r2, r3;
         ldsm_x4(kb + np * 16 * G::KPITCH + ks * 32 + k_lane, r0, r1, r2, r3);
-        mma16816<T>(sacc[2 * np], qa[ks], r0, r1);
-        mma16816<T>(sacc[2 * np + 1], qa[ks], r2, r3);
+#pragma unroll
+        for (int i = 0; i < MT; ++i) {
+          mma16816<T>(sacc[i][2 * np], qa[i], r0, r1);
+          mma16816<T>(sacc[i][2 * np + 1], qa[i], r2, r3);
+        }
       }
     }
 
     // ================= mask + online softmax =================
-    // this lane: rows h = 0 (mrow0), 1 (mrow0 + 8); columns 8 nt + 2 tig + e
-    uint32_t pa[KK][4];
-    float alpha[2];
-    {
-      // key position relative to the query position: rel = kpos_abs - qpos_abs (<= 0 when visible)
-      const int base_rel = is_ctx ? (t0 - ctx_len) : t0;  // + col - m
-      const int col_limit = is_ctx ? (ctx_len - t0) : BN;  // columns >= col_limit are past the cached prefix
+    // Only tiles that a mask edge crosses pay for the per-element tests: the last prefix tile, the causal
+    // diagonal, and tiles the sliding-window edge passes through (all CTA-uniform conditions).
+    const int base_rel = is_ctx ? (t0 - ctx_len) : t0;    // rel = base_rel + col - m  (key pos - query pos)
+    const int col_limit = is_ctx ? (ctx_len - t0) : BN;   // columns >= col_limit are past the cached prefix
+    bool need_mask;
+    if (is_ctx)
+      need_mask = (t0 + BN > ctx_len) || (W > 0 && ctx_len + m0 + BM - 1 - t0 >= W);
+    else
+      need_mask = (t0 + BN - 1 > m0) || (W > 0 && m0 + BM - 1 - t0 >= W);
+
+    uint32_t pa[MT][KK][4];
+    bool rescale = false;
+    float alpha[MT][2];
+#pragma unroll
+    for (int i = 0; i < MT; ++i) {
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        const int m = mrow0 + 8 * h;
+        const int m = wrow0 + 16 * i + gid + 8 * h;
         float mx = kNegBig;
+        if (need_mask || has_alibi) {
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
+          for (int nt = 0; nt < NT; ++nt) {
 #pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const int col = 8 * nt + 2 * tig + e;
-            const int rel = base_rel + col - m;
-            float z = sacc[nt][2 * h + e] * p.scale_log2;
-            if (has_alibi) z = fmaf(slope_l2, (float)rel, z);
-            const bool vis = col < col_limit && rel <= 0 && (W <= 0 || -rel < W);
-            z = vis ? z : kNegBig;
-            sacc[nt][2 * h + e] = z;
-            mx = fmaxf(mx, z);
+            for (int e = 0; e < 2; ++e) {
+              const int col = 8 * nt + 2 * tig + e;
+              const int rel = base_rel + col - m;
+              float z = sacc[i][nt][2 * h + e] * p.scale_log2;
+              if (has_alibi) z = fmaf(slope_l2, (float)rel, z);
+              const bool vis = !need_mask || (col < col_limit && rel <= 0 && (W <= 0 || -rel < W));
+              z = vis ? z : kNegBig;
+              sacc[i][nt][2 * h + e] = z;
+              mx = fmaxf(mx, z);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int nt = 0; nt < NT; ++nt) {
+            const float z0 = sacc[i][nt][2 * h] * p.scale_log2, z1 = sacc[i][nt][2 * h + 1] * p.scale_log2;
+            sacc[i][nt][2 * h] = z0;
+            sacc[i][nt][2 * h + 1] = z1;
+            mx = fmaxf(mx, fmaxf(z0, z1));
           }
         }
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-        const float m_new = fmaxf(m_run[h], mx);
-        alpha[h] = ex2(m_run[h] - m_new);
-        m_run[h] = m_new;
+        const float m_new = fmaxf(m_run[i][h], mx);
+        alpha[i][h] = ex2(m_run[i][h] - m_new);
+        rescale |= alpha[i][h] != 1.f;
+        m_run[i][h] = m_new;
         float sum = 0.f;
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
-          const float p0 = ex2(sacc[nt][2 * h] - m_new), p1 = ex2(sacc[nt][2 * h + 1] - m_new);
+          const float p0 = ex2(sacc[i][nt][2 * h] - m_new), p1 = ex2(sacc[i][nt][2 * h + 1] - m_new);
           sum += p0 + p1;
           // A fragment of PV: k-step nt/2; a0/a1 (rows gid/gid+8, k 2tig..) from even nt, a2/a3 from odd nt
-          pa[nt >> 1][(nt & 1) * 2 + h] = pack2<T>(p0, p1);
+          pa[i][nt >> 1][(nt & 1) * 2 + h] = pack2<T>(p0, p1);
         }
-        l_run[h] = l_run[h] * alpha[h] + sum;  // per-lane partial; quad-reduced at the end
+        l_run[i][h] = l_run[i][h] * alpha[i][h] + sum;  // per-lane partial; quad-reduced at the end
       }
     }
-    if (__any_sync(0xffffffffu, alpha[0] != 1.f || alpha[1] != 1.f)) {
+    if (__any_sync(0xffffffffu, rescale)) {
 #pragma unroll
-      for (int nd = 0; nd < ND; ++nd) {
-        oacc[nd][0] *= alpha[0];
-        oacc[nd][1] *= alpha[0];
-        oacc[nd][2] *= alpha[1];
-        oacc[nd][3] *= alpha[1];
-      }
+      for (int i = 0; i < MT; ++i)
+#pragma unroll
+        for (int nd = 0; nd < ND; ++nd) {
+          oacc[i][nd][0] *= alpha[i][0];
+          oacc[i][nd][1] *= alpha[i][0];
+          oacc[i][nd][2] *= alpha[i][1];
+          oacc[i][nd][3] *= alpha[i][1];
+        }
     }
 
     // ================= O += P V =================
@@ -353,8 +401,11 @@ __global__ void __launch_bounds__(kThreads, (DP <= 128) ? 3 : 1) context_attenti
         for (int dp = 0; dp < ND / 2; ++dp) {
           uint32_t r0, r1, r2, r3;
           ldsm_x4(vb + dp * 16 * G::VPITCH + kk * 32 + vc_lane, r0, r1, r2, r3);
-          mma16816<T>(oacc[2 * dp], pa[kk], r0, r1);
-          mma16816<T>(oacc[2 * dp + 1], pa[kk], r2, r3);
+#pragma unroll
+          for (int i = 0; i < MT; ++i) {
+            mma16816<T>(oacc[i][2 * dp], pa[i][kk], r0, r1);
+            mma16816<T>(oacc[i][2 * dp + 1], pa[i][kk], r2, r3);
+          }
         }
     } else {
 #pragma unroll
@@ -363,8 +414,11 @@ __global__ void __launch_bounds__(kThreads, (DP <= 128) ? 3 : 1) context_attenti
         for (int dp = 0; dp < ND / 2; ++dp) {
           uint32_t r0, r1, r2, r3;
           ldsm_x4_t(vb + kk * 16 * G::KPITCH + dp * 32 + vn_lane, r0, r1, r2, r3);
-          mma16816<T>(oacc[2 * dp], pa[kk], r0, r1);
-          mma16816<T>(oacc[2 * dp + 1], pa[kk], r2, r3);
+#pragma unroll
+          for (int i = 0; i < MT; ++i) {
+            mma16816<T>(oacc[i][2 * dp], pa[i][kk], r0, r1);
+            mma16816<T>(oacc[i][2 * dp + 1], pa[i][kk], r2, r3);
+          }
         }
     }
     __syncthreads();  // everyone is done with `buf` before the next iteration refills it
@@ -372,26 +426,28 @@ __global__ void __launch_bounds__(kThreads, (DP <= 128) ? 3 : 1) context_attenti
 
   // ---- epilogue ---------------------------------------------------------------------------------------
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    float l = l_run[h];
-    l += __shfl_xor_sync(0xffffffffu, l, 1);
-    l += __shfl_xor_sync(0xffffffffu, l, 2);
-    const int m = mrow0 + 8 * h;
-    if (m >= q_len) continue;
-    const float inv = 1.f / l;  // l > 0: every stored row sees at least its own key
-    T* orow = static_cast<T*>(p.out) + (tok0 + m) * p.o_stride_t + (int64_t)head * p.o_stride_h;
+  for (int i = 0; i < MT; ++i)
 #pragma unroll
-    for (int nd = 0; nd < ND; ++nd) {
-      const int d = 8 * nd + 2 * tig;
-      if (d < D) *reinterpret_cast<uint32_t*>(orow + d) = pack2<T>(oacc[nd][2 * h] * inv, oacc[nd][2 * h + 1] * inv);
+    for (int h = 0; h < 2; ++h) {
+      float l = l_run[i][h];
+      l += __shfl_xor_sync(0xffffffffu, l, 1);
+      l += __shfl_xor_sync(0xffffffffu, l, 2);
+      const int m = wrow0 + 16 * i + gid + 8 * h;
+      if (m >= q_len) continue;
+      const float inv = 1.f / l;  // l > 0: every stored row sees at least its own key
+      T* orow = static_cast<T*>(p.out) + (tok0 + m) * p.o_stride_t + (int64_t)head * p.o_stride_h;
+#pragma unroll
+      for (int nd = 0; nd < ND; ++nd) {
+        const int d = 8 * nd + 2 * tig;
+        if (d < D) *reinterpret_cast<uint32_t*>(orow + d) = pack2<T>(oacc[i][nd][2 * h] * inv, oacc[i][nd][2 * h + 1] * inv);
+      }
     }
-  }
 }
 
-template <typename T, int DP, int BN>
+template <typename T, int DP, int BN, int MT>
 static int launch(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
-  using G = Geometry<DP, BN>;
-  auto kernel = context_attention_kernel<T, DP, BN>;
+  using G = Geometry<DP, BN, MT>;
+  auto kernel = context_attention_kernel<T, DP, BN, MT>;
   static bool configured[64] = {false};
   int dev = 0;
   B200PA_CUDA_CHECK(cudaGetDevice(&dev));
@@ -399,21 +455,30 @@ static int launch(const PrefillParams& kp, int batch, int max_query_len, cudaStr
     B200PA_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM));
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
-  dim3 grid(kp.num_heads, (max_query_len + kBM - 1) / kBM, batch);
+  dim3 grid(kp.num_heads, (max_query_len + G::BM - 1) / G::BM, batch);
   kernel<<<grid, kThreads, G::SMEM, stream>>>(kp);
   B200PA_CUDA_CHECK(cudaGetLastError());
   return B200PA_OK;
 }
 
+template <typename T, int DP>
+static int launch_m(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
+  // 128-row CTAs (two m16 tiles per warp) once the queries are long enough to fill them
+  static const int force_mt = [] { const char* s = std::getenv("B200PA_PREFILL_MT"); return s ? std::atoi(s) : 0; }();
+  const bool wide = force_mt ? force_mt == 2 : max_query_len > 64;
+  if (wide) return launch<T, DP, 64, 2>(kp, batch, max_query_len, stream);
+  return launch<T, DP, 64, 1>(kp, batch, max_query_len, stream);
+}
+
 template <typename T>
 static int launch_t(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
   const int d = kp.head_size;
-  if (d <= 32) return launch<T, 32, 64>(kp, batch, max_query_len, stream);
-  if (d <= 64) return launch<T, 64, 64>(kp, batch, max_query_len, stream);
-  if (d <= 96) return launch<T, 96, 64>(kp, batch, max_query_len, stream);
-  if (d <= 128) return launch<T, 128, 64>(kp, batch, max_query_len, stream);
-  if (d <= 192) return launch<T, 192, 32>(kp, batch, max_query_len, stream);
-  return launch<T, 256, 32>(kp, batch, max_query_len, stream);
+  if (d <= 32) return launch_m<T, 32>(kp, batch, max_query_len, stream);
+  if (d <= 64) return launch_m<T, 64>(kp, batch, max_query_len, stream);
+  if (d <= 96) return launch_m<T, 96>(kp, batch, max_query_len, stream);
+  if (d <= 128) return launch_m<T, 128>(kp, batch, max_query_len, stream);
+  if (d <= 192) return launch<T, 192, 32, 1>(kp, batch, max_query_len, stream);
+  return launch<T, 256, 32, 1>(kp, batch, max_query_len, stream);
 }
 
 }  // namespace prefill
