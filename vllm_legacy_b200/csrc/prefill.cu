@@ -23,28 +23,9 @@
 #include <cstdlib>
 #include <type_traits>
 
-#include "attention_common.cuh"
+#include "prefill_common.cuh"
 
 namespace b200pa {
-
-struct PrefillParams {
-  void* out;
-  const void* q;
-  const void* k;
-  const void* v;
-  const void* k_cache;
-  const void* v_cache;
-  const int* block_tables;
-  const int* start_loc;
-  const int* seq_lens;
-  const int* ctx_lens;
-  const float* alibi_slopes;
-  int64_t q_stride_t, q_stride_h, k_stride_t, k_stride_h, v_stride_t, v_stride_h, o_stride_t, o_stride_h;
-  int64_t kc_block_stride, kc_head_stride, vc_block_stride, vc_head_stride;  // elements
-  int64_t block_table_stride;
-  int num_heads, num_kv_heads, head_size, block_shift, sliding_window;
-  float scale_log2;  // scale * log2(e)
-};
 
 namespace prefill {
 
@@ -484,6 +465,8 @@ static int launch_t(const PrefillParams& kp, int batch, int max_query_len, cudaS
 }  // namespace prefill
 }  // namespace b200pa
 
+static constexpr bool kTcDefault = true;
+
 extern "C" int b200pa_context_attention_fwd(const b200pa_prefill_params_t* a, b200pa_stream_t stream) {
   using namespace b200pa;
   if (!a) return B200PA_ERR_INVALID_ARG;
@@ -539,6 +522,14 @@ extern "C" int b200pa_context_attention_fwd(const b200pa_prefill_params_t* a, b2
   kp.block_shift = bshift;
   kp.sliding_window = a->sliding_window > 0 ? a->sliding_window : 0;
   kp.scale_log2 = a->scale * kLog2e;
+  // tcgen05 + TMEM family first (128-row CTAs; head sizes <= 128 that are multiples of 16); the mma.sync family
+  // takes short queries and every other shape.  B200PA_PREFILL_TC=0/1 forces the choice (tuning / tests).
+  static const int tc_knob = [] { const char* e = std::getenv("B200PA_PREFILL_TC"); return e ? std::atoi(e) : -1; }();
+  const bool want_tc = tc_knob >= 0 ? tc_knob != 0 : kTcDefault && a->max_query_len > 64;
+  if (want_tc) {
+    const int rc = launch_prefill_tc(kp, a->batch, a->max_query_len, a->dtype, stream);
+    if (rc != 1) return rc;
+  }
   if (a->dtype == B200PA_F16) return prefill::launch_t<__half>(kp, a->batch, a->max_query_len, stream);
   return prefill::launch_t<__nv_bfloat16>(kp, a->batch, a->max_query_len, stream);
 }

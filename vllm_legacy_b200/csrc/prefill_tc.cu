@@ -1,0 +1,493 @@
+// context_attention_fwd on the 5th-generation tensor cores (sm_100a): tcgen05.mma with the S and O accumulators
+// in Tensor Memory.  Same contract as prefill.cu (which stays the family for shapes this file does not
+// instantiate); replaces vllm/attention/ops/prefix_prefill.py:10-245, 442-681.
+//
+//   * one CTA = 128 query rows of one (sequence, query head) = the UMMA M; 128 threads, thread t owns row t
+//     (TMEM lane t), so softmax row reductions are thread-local — no shuffles;
+//   * S[128 x BN] = Q K^T : D/16 tcgen05.mma (M128 N64 K16, kind::f16, fp32 accumulate) issued by ONE thread,
+//     A = Q tile and B = K tile in shared memory in the canonical no-swizzle K-major core-matrix layout
+//     (8 rows x 16 B contiguous) — the paged K chunk [D/8][B][8] already IS that layout per block, the staging
+//     copy only re-bases the 8-token groups of several blocks to one uniform stride;
+//   * softmax: tcgen05.ld the row (32x32b), exp2 in registers, P rounded to the 16-bit type and stored to shared
+//     memory as the K-major A operand of the second MMA; the running maximum is only advanced when it grows by
+//     more than 2^8 (the O accumulator in TMEM is then rescaled through tcgen05.ld/st), so the rescale is rare;
+//   * O[128 x D] += P V : BN/16 tcgen05.mma, B = V tile K-major for the cached prefix (the paged V chunk
+//     [D][B] is token-minor) and MN-major for the new tokens ([token][d] rows) — no transposition anywhere;
+//   * K/V tiles are staged with 16-byte cp.async straight into the core-matrix layouts, double buffered; the MMAs
+//     complete on mbarriers via tcgen05.commit; two CTAs per SM overlap one CTA's softmax with the other's MMAs.
+#include <cstdlib>
+#include <type_traits>
+
+#include "prefill_common.cuh"
+
+namespace b200pa {
+namespace prefill_tc {
+
+constexpr int kThreads = 128;
+constexpr int kBM = 128;
+constexpr int kBN = 64;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "TC_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra TC_DONE;\n"
+      "bra TC_WAIT;\n"
+      "TC_DONE:\n"
+      "}" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+// MMA completion -> mbarrier (implies tcgen05.fence::before_thread_sync)
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem desc] . B[smem desc]
+__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 lanes x 32 consecutive 32-bit columns: thread i of the warp gets columns [c, c+32) of lane (base + i)
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tc_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor, no swizzle (cute/arch/mma_sm100_desc.hpp SmemDescriptor):
+// start address >> 4 in [0,14), leading byte offset >> 4 in [16,30), stride byte offset >> 4 in [32,46),
+// version = 1 in [46,48), layout type 0 (SWIZZLE_NONE) in [61,64).
+// K-major : SBO = bytes between 8-row groups (M/N direction), LBO = bytes between the two 16-byte K chunks.
+// MN-major: SBO = bytes between 8-element groups along M/N, LBO = bytes between groups of 8 K rows.
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+  return (uint64_t)((saddr >> 4) & 0x3fffu) | ((uint64_t)((lbo >> 4) & 0x3fffu) << 16) |
+         ((uint64_t)((sbo >> 4) & 0x3fffu) << 32) | (1ull << 46);
+}
+// Instruction descriptor (UMMA::InstrDescriptor): c_format F32 = 1 at [4,6), a/b format (F16 0 | BF16 1) at
+// [7,10) / [10,13), a_major [15], b_major [16] (0 = K, 1 = MN), N >> 3 at [17,23), M >> 4 at [24,29).
+template <typename T>
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int b_mn_major) {
+  const uint32_t fmt = std::is_same<T, __half>::value ? 0u : 1u;
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)b_mn_major << 16) | ((uint32_t)(N >> 3) << 17) |
+         ((uint32_t)(M >> 4) << 24);
+}
+template <typename T>
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  if constexpr (std::is_same<T, __half>::value) {
+    __half2 h = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+  } else {
+    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+}
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int DP>
+struct Geometry {
+  static constexpr int QBYTES = kBM * DP * 2;  // [D/8][128 rows][16 B]
+  static constexpr int KBYTES = kBN * DP * 2;  // [D/8][BN tokens][16 B]
+  static constexpr int VBYTES = kBN * DP * 2;  // prefix: [BN/8][D rows][16 B]; new: [BN/8][D/8][8 tokens][16 B]
+  static constexpr int PBYTES = kBM * kBN * 2; // [BN/8][128 rows][16 B]
+  static constexpr int STAGE = KBYTES + VBYTES;
+  static constexpr int SMEM = QBYTES + 2 * STAGE + PBYTES + 64;  // + barriers and the TMEM base slot
+  static constexpr int TMEM_COLS = (kBN + DP <= 128) ? 128 : 256;
+};
+
+template <typename T, int DP>
+__global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const __grid_constant__ PrefillParams p) {
+  using G = Geometry<DP>;
+  constexpr int BM = kBM, BN = kBN;
+  constexpr int DG = DP / 8;
+  extern __shared__ __align__(128) uint8_t smem[];
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+
+  const int head = blockIdx.x;
+  const int mt_idx = gridDim.y - 1 - blockIdx.y;  // heavy row tiles first
+  const int seq = blockIdx.z;
+  const int ctx_len = p.ctx_lens[seq];
+  const int q_len = p.seq_lens[seq] - ctx_len;
+  const int m0 = mt_idx * BM;
+  if (m0 >= q_len) return;  // CTA-uniform, before any allocation
+  const int64_t tok0 = p.start_loc[seq];
+  const int kv_head = head / (p.num_heads / p.num_kv_heads);
+  const int D = p.head_size;
+  const int W = p.alibi_slopes ? 0 : p.sliding_window;
+  const int bshift = p.block_shift;
+  const int B = 1 << bshift;
+
+  int c_first = 0, j_first = 0;
+  if (W > 0) {
+    c_first = max(0, ctx_len + m0 - W + 1) / BN;
+    j_first = max(0, m0 - W + 1) / BN;
+  }
+  const int c_end = (ctx_len + BN - 1) / BN;
+  const int j_end = (min(q_len, m0 + BM) + BN - 1) / BN;
+  const int n_ctx = max(0, c_end - c_first);
+  const int n_tiles = n_ctx + (j_end - j_first);
+
+  const T* kc = static_cast<const T*>(p.k_cache) + (int64_t)kv_head * p.kc_head_stride;
+  const T* vc = static_cast<const T*>(p.v_cache) + (int64_t)kv_head * p.vc_head_stride;
+  const T* kn = static_cast<const T*>(p.k) + tok0 * p.k_stride_t + (int64_t)kv_head * p.k_stride_h;
+  const T* vn = static_cast<const T*>(p.v) + tok0 * p.v_stride_t + (int64_t)kv_head * p.v_stride_h;
+  const int* table = p.block_tables + (int64_t)seq * p.block_table_stride;
+
+  const uint32_t q_smem = smem_u32(smem);
+  const uint32_t kv_smem = q_smem + G::QBYTES;
+  const uint32_t p_smem = kv_smem + 2 * G::STAGE;
+  const uint32_t bar_s = p_smem + G::PBYTES;  // 8-byte aligned: all region sizes are multiples of 128
+  const uint32_t bar_o = bar_s + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + G::QBYTES + 2 * G::STAGE + G::PBYTES + 16);
+
+  // ---- one-time setup: TMEM allocation (warp 0), mbarriers (thread 32) ----------------------------------
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "n"(G::TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  } else if (tid == 32) {
+    mbar_init(bar_s, 1);
+    mbar_init(bar_o, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+
+  // ---- staging: 16-byte cp.async straight into the UMMA core-matrix layouts ---------------------------
+  auto issue = [&](int it, int buf) {
+    const uint32_t kb = kv_smem + buf * G::STAGE;
+    const uint32_t vb = kb + G::KBYTES;
+    if (it < n_ctx) {
+      const int t0 = (c_first + it) * BN;
+      {  // K: (token t, d-group g) -> g * (BN * 16) + t * 16
+        const int t = tid % BN;
+        const int kpos = t0 + t;
+        const bool tv = kpos < ctx_len;
+        const int64_t phys = tv ? table[kpos >> bshift] : 0;
+        const T* src = kc + phys * p.kc_block_stride + (kpos & (B - 1)) * 8;
+        const uint32_t dst = kb + t * 16;
+#pragma unroll
+        for (int g = tid / BN; g < DG; g += kThreads / BN) {
+          const bool ok = tv && g * 8 < D;
+          cp_async16(dst + g * (BN * 16), ok ? (const void*)(src + (int64_t)g * B * 8) : (const void*)kc, ok ? 16 : 0);
+        }
+      }
+      {  // V: (row d, 8 tokens starting at tt) -> (tt / 8) * (DP * 16) + d * 16
+        const int rshift = min(bshift, 6);
+        const int R = 1 << rshift;
+        const int upr_shift = rshift - 3;
+        const int units_per_run = DP << upr_shift;
+#pragma unroll 4
+        for (int u = tid; u < DP * BN / 8; u += kThreads) {
+          const int run = u / units_per_run;
+          const int rem = u - run * units_per_run;
+          const int d = rem >> upr_shift;
+          const int tt = run * R + ((rem & ((1 << upr_shift) - 1)) << 3);
+          const int kpos = t0 + tt;
+          const bool ok = kpos < ctx_len && d < D;
+          const int64_t phys = ok ? table[kpos >> bshift] : 0;
+          const T* src = vc + phys * p.vc_block_stride + (int64_t)d * B + (kpos & (B - 1));
+          cp_async16(vb + (tt >> 3) * (DP * 16) + d * 16, ok ? (const void*)src : (const void*)vc, ok ? 16 : 0);
+        }
+      }
+    } else {
+      const int t0 = (j_first + it - n_ctx) * BN;
+#pragma unroll 4
+      for (int u = tid; u < BN * DG; u += kThreads) {
+        const int c = u / BN, r = u - c * BN;  // consecutive threads -> consecutive tokens of one d-group
+        const int j = t0 + r;
+        const bool ok = j < q_len && c * 8 < D;
+        // K: (token r, d-group c) -> c * (BN * 16) + r * 16   (K-major, like the prefix tiles)
+        cp_async16(kb + c * (BN * 16) + r * 16, ok ? (const void*)(kn + (int64_t)j * p.k_stride_t + c * 8) : (const void*)kn,
+                   ok ? 16 : 0);
+        // V: MN-major core matrices: 8 tokens x 16 B (8 d values); d-groups 128 B apart, token groups DP * 16 apart
+        cp_async16(vb + (r >> 3) * (DP * 16) + c * 128 + (r & 7) * 16,
+                   ok ? (const void*)(vn + (int64_t)j * p.v_stride_t + c * 8) : (const void*)vn, ok ? 16 : 0);
+      }
+    }
+  };
+
+  {  // Q: (row r, d-group c) -> c * (BM * 16) + r * 16; rows >= q_len and columns >= head_size zero-filled
+    const T* qb = static_cast<const T*>(p.q) + tok0 * p.q_stride_t + (int64_t)head * p.q_stride_h;
+#pragma unroll 4
+    for (int u = tid; u < BM * DG; u += kThreads) {
+      const int c = u / BM, r = u - c * BM;
+      const bool ok = m0 + r < q_len && c * 8 < D;
+      cp_async16(q_smem + c * (BM * 16) + r * 16, ok ? (const void*)(qb + (int64_t)(m0 + r) * p.q_stride_t + c * 8) : (const void*)qb,
+                 ok ? 16 : 0);
+    }
+  }
+  issue(0, 0);
+  cp_async_commit();
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_s = tmem_base;            // S: columns [0, BN)
+  const uint32_t tmem_o = tmem_base + BN;       // O: columns [BN, BN + DP)
+  const uint32_t lane_off = (uint32_t)(warp * 32) << 16;  // this warp's TMEM lanes
+
+  constexpr uint32_t idesc_qk = make_idesc<T>(BM, BN, 0);
+  constexpr uint32_t idesc_pv_k = make_idesc<T>(BM, DP, 0);
+  constexpr uint32_t idesc_pv_mn = make_idesc<T>(BM, DP, 1);
+
+  const float slope_l2 = p.alibi_slopes ? p.alibi_slopes[head] * kLog2e : 0.f;
+  const bool has_alibi = p.alibi_slopes != nullptr;
+  const int m = m0 + tid;  // this thread's query row
+  float m_ref = kNegBig, l_run = 0.f;
+
+  for (int it = 0; it < n_tiles; ++it) {
+    const int buf = it & 1;
+    const uint32_t ph = it & 1;
+    if (it + 1 < n_tiles) {
+      issue(it + 1, buf ^ 1);
+      cp_async_commit();
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    const uint32_t kb = kv_smem + buf * G::STAGE;
+    const uint32_t vb = kb + G::KBYTES;
+    const bool is_ctx = it < n_ctx;
+    const int t0 = is_ctx ? (c_first + it) * BN : (j_first + it - n_ctx) * BN;
+    if (is_ctx && t0 + BN > ctx_len) {
+      // last prefix tile: zero the V columns of tokens >= ctx_len (stale cache bits could be NaN; 0 * NaN = NaN)
+      __syncthreads();
+      const int nvalid = ctx_len - t0, cnt = BN - nvalid;
+      uint8_t* vrow = smem + G::QBYTES + buf * G::STAGE + G::KBYTES;
+      for (int idx = tid; idx < DP * cnt; idx += kThreads) {
+        const int d = idx / cnt, c = nvalid + (idx - d * cnt);
+        *reinterpret_cast<uint16_t*>(vrow + (c >> 3) * (DP * 16) + d * 16 + (c & 7) * 2) = 0;
+      }
+    }
+    fence_proxy_async();  // this thread's staged bytes -> visible to the tensor-core (async) proxy
+    __syncthreads();
+
+    // ================= S = Q K^T (one thread issues) =================
+    if (tid == 0) {
+      tc_fence_after();
+#pragma unroll
+      for (int ks = 0; ks < DP / 16; ++ks) {
+        const uint64_t a = make_desc(q_smem + ks * 2 * (BM * 16), BM * 16, 128);
+        const uint64_t b = make_desc(kb + ks * 2 * (BN * 16), BN * 16, 128);
+        tc_mma(tmem_s, a, b, idesc_qk, ks > 0 ? 1u : 0u);
+      }
+      tc_commit(bar_s);
+    }
+    mbar_wait(bar_s, ph);
+    tc_fence_after();
+
+    // ================= softmax on this thread's row =================
+    uint32_t sr[BN];
+    {
+      uint32_t (&lo)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sr[0]);
+      uint32_t (&hi)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sr[32]);
+      tc_ld32(tmem_s + lane_off, lo);
+      tc_ld32(tmem_s + lane_off + 32, hi);
+      tc_wait_ld();
+    }
+    const int base_rel = is_ctx ? (t0 - ctx_len) : t0;
+    const int col_limit = is_ctx ? (ctx_len - t0) : BN;
+    bool need_mask;
+    if (is_ctx)
+      need_mask = (t0 + BN > ctx_len) || (W > 0 && ctx_len + m0 + BM - 1 - t0 >= W);
+    else
+      need_mask = (t0 + BN - 1 > m0) || (W > 0 && m0 + BM - 1 - t0 >= W);
+    float mx = kNegBig;
+    if (need_mask || has_alibi) {
+#pragma unroll
+      for (int c = 0; c < BN; ++c) {
+        const int rel = base_rel + c - m;
+        float z = __uint_as_float(sr[c]) * p.scale_log2;
+        if (has_alibi) z = fmaf(slope_l2, (float)rel, z);
+        const bool vis = !need_mask || (c < col_limit && rel <= 0 && (W <= 0 || -rel < W));
+        z = vis ? z : kNegBig;
+        sr[c] = __float_as_uint(z);
+        mx = fmaxf(mx, z);
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < BN; ++c) {
+        const float z = __uint_as_float(sr[c]) * p.scale_log2;
+        sr[c] = __float_as_uint(z);
+        mx = fmaxf(mx, z);
+      }
+    }
+    // Lazy reference maximum: only move it (and rescale O in TMEM) when the row maximum grew by more than 2^8;
+    // until then p = 2^(z - m_ref) <= 256, harmless for the 16-bit P and the fp32 sums.
+    float alpha = 1.f;
+    if (mx > m_ref + 8.f) {
+      alpha = ex2(m_ref - mx);
+      m_ref = mx;
+    }
+    if (it > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
+#pragma unroll 1
+      for (int c0 = 0; c0 < DP; c0 += 32) {
+        uint32_t o[32];
+        tc_ld32(tmem_o + lane_off + c0, o);
+        tc_wait_ld();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * alpha);
+        tc_st32(tmem_o + lane_off + c0, o);
+      }
+      tc_wait_st();
+    }
+    float sum = 0.f;
+#pragma unroll
+    for (int g = 0; g < BN / 8; ++g) {
+      uint32_t w[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float p0 = ex2(__uint_as_float(sr[8 * g + 2 * j]) - m_ref);
+        const float p1 = ex2(__uint_as_float(sr[8 * g + 2 * j + 1]) - m_ref);
+        sum += p0 + p1;
+        w[j] = pack2<T>(p0, p1);
+      }
+      // P (row tid, tokens 8g..8g+7) -> K-major A operand: g * (BM * 16) + row * 16
+      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(p_smem + g * (BM * 16) + tid * 16), "r"(w[0]),
+                   "r"(w[1]), "r"(w[2]), "r"(w[3])
+                   : "memory");
+    }
+    l_run = l_run * alpha + sum;
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+
+    // ================= O += P V (one thread issues) =================
+    if (tid == 0) {
+      tc_fence_after();
+#pragma unroll
+      for (int kk = 0; kk < BN / 16; ++kk) {
+        const uint64_t a = make_desc(p_smem + kk * 2 * (BM * 16), BM * 16, 128);
+        const uint32_t acc = (it > 0 || kk > 0) ? 1u : 0u;
+        if (is_ctx) {
+          const uint64_t b = make_desc(vb + kk * 2 * (DP * 16), DP * 16, 128);
+          tc_mma(tmem_o, a, b, idesc_pv_k, acc);
+        } else {
+          const uint64_t b = make_desc(vb + kk * 2 * (DP * 16), DP * 16, 128);
+          tc_mma(tmem_o, a, b, idesc_pv_mn, acc);
+        }
+      }
+      tc_commit(bar_o);
+    }
+    mbar_wait(bar_o, ph);  // P, this K/V stage and S are free again; O is up to date
+    tc_fence_after();
+  }
+
+  // ---- epilogue: O / l -> out -------------------------------------------------------------------------
+  {
+    const float inv = 1.f / l_run;
+    T* orow = static_cast<T*>(p.out) + (tok0 + m) * p.o_stride_t + (int64_t)head * p.o_stride_h;
+#pragma unroll 1
+    for (int c0 = 0; c0 < DP; c0 += 32) {
+      uint32_t o[32];
+      tc_ld32(tmem_o + lane_off + c0, o);
+      tc_wait_ld();
+      if (m < q_len) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          if (c0 + j < D) {
+            uint4 w;
+            w.x = pack2<T>(__uint_as_float(o[j]) * inv, __uint_as_float(o[j + 1]) * inv);
+            w.y = pack2<T>(__uint_as_float(o[j + 2]) * inv, __uint_as_float(o[j + 3]) * inv);
+            w.z = pack2<T>(__uint_as_float(o[j + 4]) * inv, __uint_as_float(o[j + 5]) * inv);
+            w.w = pack2<T>(__uint_as_float(o[j + 6]) * inv, __uint_as_float(o[j + 7]) * inv);
+            *reinterpret_cast<uint4*>(orow + c0 + j) = w;
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(G::TMEM_COLS) : "memory");
+  }
+}
+
+template <typename T, int DP>
+static int launch(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
+  using G = Geometry<DP>;
+  auto kernel = context_attention_tc_kernel<T, DP>;
+  static bool configured[64] = {false};
+  int dev = 0;
+  B200PA_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    B200PA_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM));
+    if (dev >= 0 && dev < 64) configured[dev] = true;
+  }
+  dim3 grid(kp.num_heads, (max_query_len + kBM - 1) / kBM, batch);
+  kernel<<<grid, kThreads, G::SMEM, stream>>>(kp);
+  B200PA_CUDA_CHECK(cudaGetLastError());
+  return B200PA_OK;
+}
+
+}  // namespace prefill_tc
+
+int launch_prefill_tc(const PrefillParams& kp, int batch, int max_query_len, int dtype, cudaStream_t stream) {
+  auto mis16 = [](const void* ptr) { return reinterpret_cast<uintptr_t>(ptr) % 16 != 0; };
+  // 16-byte rows for the cp.async of Q and the 128-bit stores of O
+  if (mis16(kp.q) || mis16(kp.out) || kp.q_stride_t % 8 || kp.q_stride_h % 8 || kp.o_stride_t % 8 || kp.o_stride_h % 8) return 1;
+  const int d = kp.head_size;
+  if (d % 16 != 0) return 1;
+  if (dtype == B200PA_F16) {
+    if (d <= 64) return prefill_tc::launch<__half, 64>(kp, batch, max_query_len, stream);
+    if (d <= 128) return prefill_tc::launch<__half, 128>(kp, batch, max_query_len, stream);
+  } else if (dtype == B200PA_BF16) {
+    if (d <= 64) return prefill_tc::launch<__nv_bfloat16, 64>(kp, batch, max_query_len, stream);
+    if (d <= 128) return prefill_tc::launch<__nv_bfloat16, 128>(kp, batch, max_query_len, stream);
+  }
+  return 1;
+}
+
+}  // namespace b200pa
