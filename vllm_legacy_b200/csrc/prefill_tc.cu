@@ -138,11 +138,16 @@ struct Geometry {
   static constexpr int KBYTES = kBN * DP * 2;  // [D/8][BN tokens][16 B]
   static constexpr int VBYTES = kBN * DP * 2;  // prefix: [BN/8][D rows][16 B]; new: [BN/8][D/8][8 tokens][16 B]
   static constexpr int PBYTES = kBM * kBN * 2; // [BN/8][128 rows][16 B]
-  static constexpr int STAGE = KBYTES + VBYTES;
-  static constexpr int SMEM = QBYTES + 2 * STAGE + PBYTES + 64;  // + barriers and the TMEM base slot
-  static constexpr int TMEM_COLS = (kBN + DP <= 128) ? 128 : 256;
+  static constexpr int SMEM = QBYTES + 2 * KBYTES + 2 * VBYTES + PBYTES + 64;  // + barriers and the TMEM base slot
+  static constexpr int TMEM_COLS = 256;        // S0 [0,64) | S1 [64,128) | O [128, 128 + DP)
 };
 
+// Software pipeline of one CTA (tile i = 64 KV tokens):
+//   iteration i:  wait K(i+1), V(i) landed -> issue S(i+1) = Q K(i+1)^T   (tensor pipe works while we do softmax(i))
+//                 wait S(i), wait PV(i-1)  -> issue cp.async K(i+2), V(i+1)
+//                 softmax(i) from TMEM, P(i) -> shared                    -> issue O += P(i) V(i), no wait
+// so the tensor pipe always has the next QK^T queued behind the current PV, and the copies of a tile have a
+// whole iteration to land.  S is double buffered in TMEM, K and V each double buffered in shared memory.
 template <typename T, int DP>
 __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const __grid_constant__ PrefillParams p) {
   using G = Geometry<DP>;
@@ -184,11 +189,13 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
   const int* table = p.block_tables + (int64_t)seq * p.block_table_stride;
 
   const uint32_t q_smem = smem_u32(smem);
-  const uint32_t kv_smem = q_smem + G::QBYTES;
-  const uint32_t p_smem = kv_smem + 2 * G::STAGE;
-  const uint32_t bar_s = p_smem + G::PBYTES;  // 8-byte aligned: all region sizes are multiples of 128
-  const uint32_t bar_o = bar_s + 8;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + G::QBYTES + 2 * G::STAGE + G::PBYTES + 16);
+  const uint32_t k_smem = q_smem + G::QBYTES;
+  const uint32_t v_smem = k_smem + 2 * G::KBYTES;
+  const uint32_t p_smem = v_smem + 2 * G::VBYTES;
+  const uint32_t bar_s = p_smem + G::PBYTES;  // two barriers (S0, S1); 8-byte aligned: region sizes are multiples of 128
+  const uint32_t bar_o = bar_s + 16;
+  constexpr int kSlotOff = G::QBYTES + 2 * G::KBYTES + 2 * G::VBYTES + G::PBYTES + 32;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kSlotOff);
 
   // ---- one-time setup: TMEM allocation (warp 0), mbarriers (thread 32) ----------------------------------
   if (warp == 0) {
@@ -198,88 +205,113 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   } else if (tid == 32) {
     mbar_init(bar_s, 1);
+    mbar_init(bar_s + 8, 1);
     mbar_init(bar_o, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
 
   // ---- staging: 16-byte cp.async straight into the UMMA core-matrix layouts ---------------------------
-  auto issue = [&](int it, int buf) {
-    const uint32_t kb = kv_smem + buf * G::STAGE;
-    const uint32_t vb = kb + G::KBYTES;
+  // Every thread always copies the same token (K: tid % 64; cached V: the 8-token group tid % 8), so it needs
+  // ONE block-table entry per tile and copy kind; those are fetched one pipeline step ahead (phys_k / phys_v).
+  const int kt = tid % BN;        // K / new-V token inside the tile
+  const int vg = (tid & 7) * 8;   // first token of this thread's 8-token group (cached V)
+  auto k_entry = [&](int it) -> int {  // physical block of this thread's K token in tile `it` (prefix tiles only)
+    const int kpos = (c_first + it) * BN + kt;
+    return (it < n_ctx && kpos < ctx_len) ? table[kpos >> bshift] : -1;
+  };
+  auto v_entry = [&](int it) -> int {
+    const int kpos = (c_first + it) * BN + vg;
+    return (it < n_ctx && kpos < ctx_len) ? table[kpos >> bshift] : -1;
+  };
+  auto load_k = [&](int it, int phys) {
+    if (it >= n_tiles) return;
+    const uint32_t dst = k_smem + (it & 1) * G::KBYTES + kt * 16;  // (token t, d-group g) -> g * (BN * 16) + t * 16
     if (it < n_ctx) {
-      const int t0 = (c_first + it) * BN;
-      {  // K: (token t, d-group g) -> g * (BN * 16) + t * 16
-        const int t = tid % BN;
-        const int kpos = t0 + t;
-        const bool tv = kpos < ctx_len;
-        const int64_t phys = tv ? table[kpos >> bshift] : 0;
-        const T* src = kc + phys * p.kc_block_stride + (kpos & (B - 1)) * 8;
-        const uint32_t dst = kb + t * 16;
+      const int kpos = (c_first + it) * BN + kt;
+      const T* src = kc + (int64_t)max(phys, 0) * p.kc_block_stride + (kpos & (B - 1)) * 8;
 #pragma unroll
-        for (int g = tid / BN; g < DG; g += kThreads / BN) {
-          const bool ok = tv && g * 8 < D;
-          cp_async16(dst + g * (BN * 16), ok ? (const void*)(src + (int64_t)g * B * 8) : (const void*)kc, ok ? 16 : 0);
-        }
-      }
-      {  // V: (row d, 8 tokens starting at tt) -> (tt / 8) * (DP * 16) + d * 16
-        const int rshift = min(bshift, 6);
-        const int R = 1 << rshift;
-        const int upr_shift = rshift - 3;
-        const int units_per_run = DP << upr_shift;
-#pragma unroll 4
-        for (int u = tid; u < DP * BN / 8; u += kThreads) {
-          const int run = u / units_per_run;
-          const int rem = u - run * units_per_run;
-          const int d = rem >> upr_shift;
-          const int tt = run * R + ((rem & ((1 << upr_shift) - 1)) << 3);
-          const int kpos = t0 + tt;
-          const bool ok = kpos < ctx_len && d < D;
-          const int64_t phys = ok ? table[kpos >> bshift] : 0;
-          const T* src = vc + phys * p.vc_block_stride + (int64_t)d * B + (kpos & (B - 1));
-          cp_async16(vb + (tt >> 3) * (DP * 16) + d * 16, ok ? (const void*)src : (const void*)vc, ok ? 16 : 0);
-        }
+      for (int g = tid / BN; g < DG; g += kThreads / BN) {
+        const bool ok = phys >= 0 && g * 8 < D;
+        cp_async16(dst + g * (BN * 16), ok ? (const void*)(src + (int64_t)g * B * 8) : (const void*)kc, ok ? 16 : 0);
       }
     } else {
-      const int t0 = (j_first + it - n_ctx) * BN;
-#pragma unroll 4
-      for (int u = tid; u < BN * DG; u += kThreads) {
-        const int c = u / BN, r = u - c * BN;  // consecutive threads -> consecutive tokens of one d-group
-        const int j = t0 + r;
-        const bool ok = j < q_len && c * 8 < D;
-        // K: (token r, d-group c) -> c * (BN * 16) + r * 16   (K-major, like the prefix tiles)
-        cp_async16(kb + c * (BN * 16) + r * 16, ok ? (const void*)(kn + (int64_t)j * p.k_stride_t + c * 8) : (const void*)kn,
-                   ok ? 16 : 0);
-        // V: MN-major core matrices: 8 tokens x 16 B (8 d values); d-groups 128 B apart, token groups DP * 16 apart
-        cp_async16(vb + (r >> 3) * (DP * 16) + c * 128 + (r & 7) * 16,
-                   ok ? (const void*)(vn + (int64_t)j * p.v_stride_t + c * 8) : (const void*)vn, ok ? 16 : 0);
+      const int j = (j_first + it - n_ctx) * BN + kt;
+      const T* src = kn + (int64_t)j * p.k_stride_t;
+#pragma unroll
+      for (int g = tid / BN; g < DG; g += kThreads / BN) {
+        const bool ok = j < q_len && g * 8 < D;
+        cp_async16(dst + g * (BN * 16), ok ? (const void*)(src + g * 8) : (const void*)kn, ok ? 16 : 0);
+      }
+    }
+  };
+  auto load_v = [&](int it, int phys) {
+    if (it >= n_tiles) return;
+    const uint32_t vb = v_smem + (it & 1) * G::VBYTES;
+    if (it < n_ctx) {
+      // (row d, 8 tokens starting at vg) -> (vg / 8) * (DP * 16) + d * 16     [K-major B operand, N = d]
+      const int kpos = (c_first + it) * BN + vg;
+      const T* src = vc + (int64_t)max(phys, 0) * p.vc_block_stride + (kpos & (B - 1));
+      const uint32_t dst = vb + (vg >> 3) * (DP * 16);
+#pragma unroll
+      for (int d = tid >> 3; d < DP; d += kThreads / 8) {
+        const bool ok = phys >= 0 && d < D;
+        cp_async16(dst + d * 16, ok ? (const void*)(src + (int64_t)d * B) : (const void*)vc, ok ? 16 : 0);
+      }
+    } else {
+      // MN-major core matrices: 8 tokens x 16 B (8 d values); d-groups 128 B apart, token groups DP * 16 apart
+      const int j = (j_first + it - n_ctx) * BN + kt;
+      const T* src = vn + (int64_t)j * p.v_stride_t;
+      const uint32_t dst = vb + (kt >> 3) * (DP * 16) + (kt & 7) * 16;
+#pragma unroll
+      for (int g = tid / BN; g < DG; g += kThreads / BN) {
+        const bool ok = j < q_len && g * 8 < D;
+        cp_async16(dst + g * 128, ok ? (const void*)(src + g * 8) : (const void*)vn, ok ? 16 : 0);
       }
     }
   };
 
   {  // Q: (row r, d-group c) -> c * (BM * 16) + r * 16; rows >= q_len and columns >= head_size zero-filled
     const T* qb = static_cast<const T*>(p.q) + tok0 * p.q_stride_t + (int64_t)head * p.q_stride_h;
-#pragma unroll 4
-    for (int u = tid; u < BM * DG; u += kThreads) {
-      const int c = u / BM, r = u - c * BM;
-      const bool ok = m0 + r < q_len && c * 8 < D;
-      cp_async16(q_smem + c * (BM * 16) + r * 16, ok ? (const void*)(qb + (int64_t)(m0 + r) * p.q_stride_t + c * 8) : (const void*)qb,
-                 ok ? 16 : 0);
+    const bool rv = m0 + tid < q_len;
+    const T* src = qb + (int64_t)(m0 + tid) * p.q_stride_t;
+#pragma unroll
+    for (int c = 0; c < DG; ++c) {
+      const bool ok = rv && c * 8 < D;
+      cp_async16(q_smem + c * (BM * 16) + tid * 16, ok ? (const void*)(src + c * 8) : (const void*)qb, ok ? 16 : 0);
     }
   }
-  issue(0, 0);
-  cp_async_commit();
+  load_k(0, k_entry(0));
+  cp_async_commit();               // group: Q, K(0)
+  load_k(1, k_entry(1));
+  load_v(0, v_entry(0));
+  cp_async_commit();               // group: K(1), V(0)
+  int phys_k = k_entry(2);         // for the copies issued in iteration 0
+  int phys_v = v_entry(1);
 
+  cp_async_wait<1>();  // Q, K(0)
+  fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_s = tmem_base;            // S: columns [0, BN)
-  const uint32_t tmem_o = tmem_base + BN;       // O: columns [BN, BN + DP)
-  const uint32_t lane_off = (uint32_t)(warp * 32) << 16;  // this warp's TMEM lanes
+  const uint32_t tmem_o = tmem_base + 2 * BN;              // O: columns [128, 128 + DP)
+  const uint32_t lane_off = (uint32_t)(warp * 32) << 16;   // this warp's TMEM lanes
 
   constexpr uint32_t idesc_qk = make_idesc<T>(BM, BN, 0);
   constexpr uint32_t idesc_pv_k = make_idesc<T>(BM, DP, 0);
   constexpr uint32_t idesc_pv_mn = make_idesc<T>(BM, DP, 1);
+
+  auto issue_qk = [&](int it) {  // S(it & 1) = Q K(it)^T   (one thread)
+    const uint32_t kb = k_smem + (it & 1) * G::KBYTES;
+#pragma unroll
+    for (int ks = 0; ks < DP / 16; ++ks) {
+      const uint64_t a = make_desc(q_smem + ks * 2 * (BM * 16), BM * 16, 128);
+      const uint64_t b = make_desc(kb + ks * 2 * (BN * 16), BN * 16, 128);
+      tc_mma(tmem_base + (it & 1) * BN, a, b, idesc_qk, ks > 0 ? 1u : 0u);
+    }
+    tc_commit(bar_s + 8 * (it & 1));
+  };
+  if (tid == 0) issue_qk(0);
 
   const float slope_l2 = p.alibi_slopes ? p.alibi_slopes[head] * kLog2e : 0.f;
   const bool has_alibi = p.alibi_slopes != nullptr;
@@ -287,24 +319,17 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
   float m_ref = kNegBig, l_run = 0.f;
 
   for (int it = 0; it < n_tiles; ++it) {
-    const int buf = it & 1;
-    const uint32_t ph = it & 1;
-    if (it + 1 < n_tiles) {
-      issue(it + 1, buf ^ 1);
-      cp_async_commit();
-      cp_async_wait<1>();
-    } else {
-      cp_async_wait<0>();
-    }
-    const uint32_t kb = kv_smem + buf * G::STAGE;
-    const uint32_t vb = kb + G::KBYTES;
     const bool is_ctx = it < n_ctx;
     const int t0 = is_ctx ? (c_first + it) * BN : (j_first + it - n_ctx) * BN;
+    const uint32_t vb = v_smem + (it & 1) * G::VBYTES;
+
+    // ---- (a) K(it+1) and V(it) have landed ----------------------------------------------------------
+    cp_async_wait<0>();
     if (is_ctx && t0 + BN > ctx_len) {
       // last prefix tile: zero the V columns of tokens >= ctx_len (stale cache bits could be NaN; 0 * NaN = NaN)
       __syncthreads();
       const int nvalid = ctx_len - t0, cnt = BN - nvalid;
-      uint8_t* vrow = smem + G::QBYTES + buf * G::STAGE + G::KBYTES;
+      uint8_t* vrow = smem + G::QBYTES + 2 * G::KBYTES + (it & 1) * G::VBYTES;
       for (int idx = tid; idx < DP * cnt; idx += kThreads) {
         const int d = idx / cnt, c = nvalid + (idx - d * cnt);
         *reinterpret_cast<uint16_t*>(vrow + (c >> 3) * (DP * 16) + d * 16 + (c & 7) * 2) = 0;
@@ -313,27 +338,31 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
     fence_proxy_async();  // this thread's staged bytes -> visible to the tensor-core (async) proxy
     __syncthreads();
 
-    // ================= S = Q K^T (one thread issues) =================
-    if (tid == 0) {
+    // ---- (b) queue the NEXT tile's QK^T behind the previous PV ------------------------------------------
+    if (tid == 0 && it + 1 < n_tiles) {
       tc_fence_after();
-#pragma unroll
-      for (int ks = 0; ks < DP / 16; ++ks) {
-        const uint64_t a = make_desc(q_smem + ks * 2 * (BM * 16), BM * 16, 128);
-        const uint64_t b = make_desc(kb + ks * 2 * (BN * 16), BN * 16, 128);
-        tc_mma(tmem_s, a, b, idesc_qk, ks > 0 ? 1u : 0u);
-      }
-      tc_commit(bar_s);
+      issue_qk(it + 1);
     }
-    mbar_wait(bar_s, ph);
+    // ---- (c, d) S(it) ready; PV(it-1) done: P, V(it-1)'s stage and O are ours again ------------------
+    mbar_wait(bar_s + 8 * (it & 1), (it >> 1) & 1);
+    if (it > 0) mbar_wait(bar_o, (it - 1) & 1);
     tc_fence_after();
 
-    // ================= softmax on this thread's row =================
+    // ---- (e) copies for the following iteration --------------------------------------------------------
+    load_k(it + 2, phys_k);
+    load_v(it + 1, phys_v);
+    cp_async_commit();
+    phys_k = k_entry(it + 3);
+    phys_v = v_entry(it + 2);
+
+    // ---- (f) softmax on this thread's row ------------------------------------------------------------
     uint32_t sr[BN];
     {
       uint32_t (&lo)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sr[0]);
       uint32_t (&hi)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sr[32]);
-      tc_ld32(tmem_s + lane_off, lo);
-      tc_ld32(tmem_s + lane_off + 32, hi);
+      const uint32_t ts = tmem_base + (it & 1) * BN + lane_off;
+      tc_ld32(ts, lo);
+      tc_ld32(ts + 32, hi);
       tc_wait_ld();
     }
     const int base_rel = is_ctx ? (t0 - ctx_len) : t0;
@@ -344,6 +373,7 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
     else
       need_mask = (t0 + BN - 1 > m0) || (W > 0 && m0 + BM - 1 - t0 >= W);
     float mx = kNegBig;
+    float mult;  // p = 2^(sr * mult - m_ref)
     if (need_mask || has_alibi) {
 #pragma unroll
       for (int c = 0; c < BN; ++c) {
@@ -355,13 +385,12 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
         sr[c] = __float_as_uint(z);
         mx = fmaxf(mx, z);
       }
-    } else {
+      mult = 1.f;
+    } else {  // interior tile: the maximum commutes with the (positive) scale, which then rides in the FFMA
 #pragma unroll
-      for (int c = 0; c < BN; ++c) {
-        const float z = __uint_as_float(sr[c]) * p.scale_log2;
-        sr[c] = __float_as_uint(z);
-        mx = fmaxf(mx, z);
-      }
+      for (int c = 0; c < BN; ++c) mx = fmaxf(mx, __uint_as_float(sr[c]));
+      mx *= p.scale_log2;
+      mult = p.scale_log2;
     }
     // Lazy reference maximum: only move it (and rescale O in TMEM) when the row maximum grew by more than 2^8;
     // until then p = 2^(z - m_ref) <= 256, harmless for the 16-bit P and the fp32 sums.
@@ -383,13 +412,14 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
       tc_wait_st();
     }
     float sum = 0.f;
+    const float neg_ref = -m_ref;
 #pragma unroll
     for (int g = 0; g < BN / 8; ++g) {
       uint32_t w[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float p0 = ex2(__uint_as_float(sr[8 * g + 2 * j]) - m_ref);
-        const float p1 = ex2(__uint_as_float(sr[8 * g + 2 * j + 1]) - m_ref);
+        const float p0 = ex2(fmaf(__uint_as_float(sr[8 * g + 2 * j]), mult, neg_ref));
+        const float p1 = ex2(fmaf(__uint_as_float(sr[8 * g + 2 * j + 1]), mult, neg_ref));
         sum += p0 + p1;
         w[j] = pack2<T>(p0, p1);
       }
@@ -403,26 +433,20 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
     tc_fence_before();
     __syncthreads();
 
-    // ================= O += P V (one thread issues) =================
+    // ---- (g) O += P V (one thread issues; nobody waits here) -------------------------------------------
     if (tid == 0) {
       tc_fence_after();
 #pragma unroll
       for (int kk = 0; kk < BN / 16; ++kk) {
         const uint64_t a = make_desc(p_smem + kk * 2 * (BM * 16), BM * 16, 128);
-        const uint32_t acc = (it > 0 || kk > 0) ? 1u : 0u;
-        if (is_ctx) {
-          const uint64_t b = make_desc(vb + kk * 2 * (DP * 16), DP * 16, 128);
-          tc_mma(tmem_o, a, b, idesc_pv_k, acc);
-        } else {
-          const uint64_t b = make_desc(vb + kk * 2 * (DP * 16), DP * 16, 128);
-          tc_mma(tmem_o, a, b, idesc_pv_mn, acc);
-        }
+        const uint64_t b = make_desc(vb + kk * 2 * (DP * 16), DP * 16, 128);
+        tc_mma(tmem_o, a, b, is_ctx ? idesc_pv_k : idesc_pv_mn, (it > 0 || kk > 0) ? 1u : 0u);
       }
       tc_commit(bar_o);
     }
-    mbar_wait(bar_o, ph);  // P, this K/V stage and S are free again; O is up to date
-    tc_fence_after();
   }
+  mbar_wait(bar_o, (n_tiles - 1) & 1);
+  tc_fence_after();
 
   // ---- epilogue: O / l -> out -------------------------------------------------------------------------
   {
