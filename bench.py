@@ -247,6 +247,44 @@ def run_ours(args, rank, world, local_rank):
     return line
 
 
+def prefill_extra(dev, iters=10):
+    """Extra, outside the headline metric: the tcgen05 prefix-prefill kernel on a Llama-3-8B
+    chunked-prefill shape (8 sequences x 2048 new tokens over 4096 cached tokens, 32q/8kv, head 128, block 16, bf16),
+    timed with CUDA events, reported against the MEASURED cuBLAS bf16 peak (tensor roofline)."""
+    from tests import helpers
+    from vllm_legacy_b200 import _custom_ops as ops
+    Hq, qpk, D, B = 32, 4, 128, 16
+    case = helpers.make_prefill_case(Hq, qpk, D, torch.bfloat16, dev, block_size=B, amplitude=1.0,
+                                     query_lens=[2048] * 8, ctx_lens=[4096] * 8)
+    flops = 4.0 * D * Hq * sum(q * c + q * (q + 1) / 2 for q, c in zip(case["query_lens"], case["ctx_lens"]))
+    out = torch.empty_like(case["query"])
+    a = (case["query"], case["k"], case["v"], out, case["k_cache"], case["v_cache"], case["block_table"],
+         case["b_start_loc"], case["b_seq_len"], case["b_ctx_len"], case["max_input_len"], None, 0)
+    for _ in range(3):
+        ops.context_attention_fwd(*a)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        ops.context_attention_fwd(*a)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    tflops = flops / ms / 1e9
+    peak = None
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peak = float(json.load(f)["bf16_tflops"])
+    except Exception:  # noqa: BLE001
+        pass
+    return {"op": "context_attention_fwd (tcgen05 + TMEM prefix-prefill kernel)",
+            "workload": "8 seqs x 2048 new tokens over 4096 cached, 32q/8kv, head 128, block 16, bf16",
+            "ms": round(ms, 4), "algorithmic_tflops": round(tflops, 1), "launches": iters,
+            "roofline": {"bound": "tensor", "achieved": round(tflops, 1), "peak": peak, "unit": "TFLOP/s",
+                         "frac": round(tflops / peak, 4) if peak else None,
+                         "peak_source": "measured (MEASURED_PEAKS.json bf16_tflops, cuBLAS burst)"}}
+
+
 # ------------------------------------------------------------------------------------------------
 # reference arm: the reference's own CPU kernels (oracle/_ref) on the host cores
 # ------------------------------------------------------------------------------------------------
@@ -349,6 +387,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU baseline leg (profiling runs)")
+    ap.add_argument("--no-extra", action="store_true", help="skip the extra (non-headline) prefill measurement")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -371,6 +410,11 @@ def main():
     try:
         line = run_ours(args, rank, world, local_rank)
         if rank == 0:
+            if world == 1 and not args.no_extra:
+                try:
+                    line["extra"] = {"prefill": prefill_extra(torch.device("cuda", local_rank))}
+                except Exception as e:  # noqa: BLE001
+                    line["extra"] = {"prefill": {"failed": str(e)[:200]}}
             if world == 1 and not args.no_cpu_baseline:
                 try:
                     gbps, desc = cpu_reference_run(total_budget_s=15.0, steps=3, warmup=1)

@@ -234,7 +234,7 @@ int oracle_reshape_and_cache_flash(const void* key, const void* value, void* k_c
  * (2i, 2i+1) with cos[i], sin[i]; arr[x] = x*cos - y*sin; arr[y] = y*cos + x*sin evaluated with
  * scalar_t operators: for c10::Half / c10::BFloat16 every product and sum is computed in fp32 and
  * rounded back to the 16-bit type (torch/headeronly/util/Half.h:501-511, BFloat16.h:185-198); for
- * float nvcc contracts to fma(x, cos, -(y*sin)) and fma(y, cos, x*sin) (SASS of the reference
+ * float nvcc contracts to fma(x, cos, -(y*sin)) and fma(x, sin, y*cos) (SASS of the reference
  * build: FMUL, FMUL, FFMA, FFMA).  offsets == NULL: rotary_embedding (:70-93), else the batched
  * form (:95-131) with cache row pos + offset.
  * --------------------------------------------------------------------------------------------- */
@@ -243,7 +243,7 @@ static void rotate_pair(void* arr, int64_t xi, int64_t yi, float c, float s, int
   float nx, ny;
   if (dt == DT_F32) {
     nx = fmaf(x, c, -(y * s));
-    ny = fmaf(y, c, x * s);
+    ny = fmaf(x, s, y * c);
   } else {
     nx = round_to(x * c, dt) - round_to(y * s, dt);
     ny = round_to(y * c, dt) + round_to(x * s, dt);

@@ -8,7 +8,7 @@ timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smok
 timeout 600 python bench.py --steps 200 --warmup 10 > gpurun_out/bench_ours.json 2> gpurun_out/bench_ours.err; echo "exit=$?" >> gpurun_out/bench_ours.err
 timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
 nproc > gpurun_out/host.txt; lscpu | head -20 >> gpurun_out/host.txt; nvidia-smi >> gpurun_out/host.txt
-CMD="python bench.py --steps 20 --warmup 3 --no-cpu-baseline"
+CMD="python bench.py --steps 20 --warmup 3 --no-cpu-baseline --no-extra"
 timeout 300 $CMD > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
 timeout 300 $CMD > gpurun_out/plain2.log 2>&1 && \

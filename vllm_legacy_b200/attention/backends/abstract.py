@@ -1,106 +1,92 @@
-"""Attention backend interface — the ABCs of the reference's
-`vllm/attention/backends/abstract.py:9-133` (including the fork's extra `rope_*` /
-`position_ids` keyword arguments on `AttentionImpl.forward`, :119-133), restated so backends
-written against the reference type-check against this package unchanged."""
-from abc import ABC, abstractmethod
-from dataclasses import dataclass, fields
+"""Attention backend interface of this package.
+
+Same three contracts, names and call signatures as the reference's `vllm/attention/backends/abstract.py:9-133`
+(including the fork's extra `rope_method` / `rope_cos` / `rope_sin` / `position_ids` keywords on
+`AttentionImpl.forward`, :119-133), so a backend written against the reference also satisfies these ABCs.
+Written for this package: the interface is what is shared, not the text.
+"""
+import abc
+import dataclasses
 from typing import Any, Dict, Generic, List, Literal, Optional, Set, Tuple, Type, TypeVar
 
 import torch
 
-
-class AttentionBackend(ABC):
-    """Abstract class for attention backends."""
-
-    @staticmethod
-    @abstractmethod
-    def get_name() -> str:
-        raise NotImplementedError
-
-    @staticmethod
-    @abstractmethod
-    def get_impl_cls() -> Type["AttentionImpl"]:
-        raise NotImplementedError
-
-    @staticmethod
-    @abstractmethod
-    def make_metadata(*args, **kwargs) -> "AttentionMetadata":
-        raise NotImplementedError
-
-    @staticmethod
-    @abstractmethod
-    def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int,
-                           head_size: int) -> Tuple[int, ...]:
-        raise NotImplementedError
-
-    @staticmethod
-    @abstractmethod
-    def swap_blocks(src_kv_cache: torch.Tensor, dst_kv_cache: torch.Tensor,
-                    src_to_dst: torch.Tensor) -> None:
-        raise NotImplementedError
-
-    @staticmethod
-    @abstractmethod
-    def copy_blocks(kv_caches: List[torch.Tensor], src_to_dists: torch.Tensor) -> None:
-        raise NotImplementedError
+KVCacheShape = Tuple[int, ...]
 
 
-@dataclass
+def _required(fn):
+    """Abstract static hook: subclasses must override it; calling the base raises."""
+    return staticmethod(abc.abstractmethod(fn))
+
+
+@dataclasses.dataclass
 class AttentionMetadata:
-    """Attention metadata for prefill and decode batched together."""
-    num_prefills: int
-    num_prefill_tokens: int
-    num_decode_tokens: int
-    # (num_tokens,) slot of every input token in the paged cache; < 0 = padding.
-    slot_mapping: torch.Tensor
+    """Per-step metadata of a batch laid out as [prefill tokens | decode tokens]."""
+    num_prefills: int          # prompt sequences in the batch
+    num_prefill_tokens: int    # their tokens (rows 0 .. num_prefill_tokens - 1)
+    num_decode_tokens: int     # one row per decoding sequence, after the prefill rows
+    slot_mapping: torch.Tensor  # [num_tokens] paged-cache slot of every row; negative = padding row
 
     @property
-    @abstractmethod
+    @abc.abstractmethod
     def prefill_metadata(self) -> Optional["AttentionMetadata"]:
-        pass
+        """View restricted to the prefill rows, or None when the batch has none."""
 
     @property
-    @abstractmethod
+    @abc.abstractmethod
     def decode_metadata(self) -> Optional["AttentionMetadata"]:
-        pass
+        """View restricted to the decode rows, or None when the batch has none."""
 
     def asdict_zerocopy(self, skip_fields: Optional[Set[str]] = None) -> Dict[str, Any]:
-        if skip_fields is None:
-            skip_fields = set()
-        return {f.name: getattr(self, f.name) for f in fields(self) if f.name not in skip_fields}
+        """Field name -> the very object stored (no deep copy as dataclasses.asdict would make)."""
+        skip = skip_fields or set()
+        return {f.name: getattr(self, f.name) for f in dataclasses.fields(self) if f.name not in skip}
 
 
 T = TypeVar("T", bound=AttentionMetadata)
 
 
-class AttentionImpl(ABC, Generic[T]):
+class AttentionImpl(abc.ABC, Generic[T]):
+    """One attention layer's kernel-facing object: built once per layer, called every step."""
 
-    @abstractmethod
-    def __init__(
-        self,
-        num_heads: int,
-        head_size: int,
-        scale: float,
-        num_kv_heads: Optional[int] = None,
-        alibi_slopes: Optional[List[float]] = None,
-        sliding_window: Optional[int] = None,
-        kv_cache_dtype: str = "auto",
-        blocksparse_params: Optional[Dict[str, Any]] = None,
-    ) -> None:
+    @abc.abstractmethod
+    def __init__(self, num_heads: int, head_size: int, scale: float, num_kv_heads: Optional[int] = None,
+                 alibi_slopes: Optional[List[float]] = None, sliding_window: Optional[int] = None,
+                 kv_cache_dtype: str = "auto", blocksparse_params: Optional[Dict[str, Any]] = None) -> None:
         raise NotImplementedError
 
-    @abstractmethod
-    def forward(
-        self,
-        query: torch.Tensor,
-        key: torch.Tensor,
-        value: torch.Tensor,
-        kv_cache: torch.Tensor,
-        attn_metadata: T,
-        kv_scale: float = 1.0,
-        rope_method: Literal['none', 'self_extend'] = 'none',
-        rope_cos: Optional[torch.Tensor] = None,
-        rope_sin: Optional[torch.Tensor] = None,
-        position_ids: Optional[torch.Tensor] = None,
-    ) -> torch.Tensor:
+    @abc.abstractmethod
+    def forward(self, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, kv_cache: torch.Tensor,
+                attn_metadata: T, kv_scale: float = 1.0,
+                rope_method: Literal['none', 'self_extend'] = 'none', rope_cos: Optional[torch.Tensor] = None,
+                rope_sin: Optional[torch.Tensor] = None,
+                position_ids: Optional[torch.Tensor] = None) -> torch.Tensor:
+        raise NotImplementedError
+
+
+class AttentionBackend(abc.ABC):
+    """Factory + cache-layout owner a model runner talks to; every hook is a static method."""
+
+    @_required
+    def get_name() -> str:
+        raise NotImplementedError
+
+    @_required
+    def get_impl_cls() -> Type[AttentionImpl]:
+        raise NotImplementedError
+
+    @_required
+    def make_metadata(*args, **kwargs) -> AttentionMetadata:
+        raise NotImplementedError
+
+    @_required
+    def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int, head_size: int) -> KVCacheShape:
+        raise NotImplementedError
+
+    @_required
+    def swap_blocks(src_kv_cache: torch.Tensor, dst_kv_cache: torch.Tensor, src_to_dst: torch.Tensor) -> None:
+        raise NotImplementedError
+
+    @_required
+    def copy_blocks(kv_caches: List[torch.Tensor], src_to_dists: torch.Tensor) -> None:
         raise NotImplementedError

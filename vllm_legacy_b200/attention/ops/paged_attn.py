@@ -56,93 +56,60 @@ class PagedAttention:
                               kv_cache_dtype, kv_scale)
 
     @staticmethod
-    def forward_decode(
-        query: torch.Tensor,
-        key_cache: torch.Tensor,
-        value_cache: torch.Tensor,
-        block_tables: torch.Tensor,
-        seq_lens: torch.Tensor,
-        max_seq_len: int,
-        kv_cache_dtype: str,
-        num_kv_heads: int,
-        scale: float,
-        alibi_slopes: Optional[torch.Tensor],
-        kv_scale: float,
-        tp_rank: int = 0,
-        blocksparse_local_blocks: int = 0,
-        blocksparse_vert_stride: int = 0,
-        blocksparse_block_size: int = 64,
-        blocksparse_head_sliding_step: int = 0,
-    ) -> torch.Tensor:
-        if blocksparse_vert_stride is not None and blocksparse_vert_stride > 1:
-            block_size = value_cache.size(-1)
-            assert (blocksparse_block_size > 0 and blocksparse_block_size % block_size == 0), \
-                (f"{blocksparse_block_size=} needs to be a multiple of"
-                 f"{block_size=} used in block_tables.")
-
-        output = torch.empty_like(query)
-        block_size = value_cache.shape[3]
-        num_seqs, num_heads, head_size = query.shape
-        max_num_partitions = (max_seq_len + _PARTITION_SIZE - 1) // _PARTITION_SIZE
-        # Reference heuristic, kept verbatim in meaning (paged_attn.py:112-121): V1 when one
-        # partition suffices or there are many (sequence, head) pairs, V2 above 8192 tokens.
-        use_v1 = (max_seq_len <= 8192 and (max_num_partitions == 1 or num_seqs * num_heads > 512))
-
-        if use_v1:
-            ops.paged_attention_v1(output, query, key_cache, value_cache, num_kv_heads, scale,
-                                   block_tables, seq_lens, block_size, max_seq_len, alibi_slopes,
-                                   kv_cache_dtype, kv_scale, tp_rank, blocksparse_local_blocks,
-                                   blocksparse_vert_stride, blocksparse_block_size,
-                                   blocksparse_head_sliding_step)
-        else:
-            assert _PARTITION_SIZE % block_size == 0
-            tmp_output = torch.empty(size=(num_seqs, num_heads, max_num_partitions, head_size),
-                                     dtype=output.dtype, device=output.device)
-            exp_sums = torch.empty(size=(num_seqs, num_heads, max_num_partitions),
-                                   dtype=torch.float32, device=output.device)
-            max_logits = torch.empty_like(exp_sums)
-            ops.paged_attention_v2(output, exp_sums, max_logits, tmp_output, query, key_cache,
-                                   value_cache, num_kv_heads, scale, block_tables, seq_lens,
-                                   block_size, max_seq_len, alibi_slopes, kv_cache_dtype, kv_scale,
-                                   tp_rank, blocksparse_local_blocks, blocksparse_vert_stride,
-                                   blocksparse_block_size, blocksparse_head_sliding_step)
-        return output
+    def _partitions(max_seq_len: int) -> int:
+        """Scratch partitions the callers size for v2: ceil(max_seq_len / 512) (paged_attn.py:111)."""
+        return -(-max_seq_len // _PARTITION_SIZE)
 
     @staticmethod
-    def forward_prefix(
-        query: torch.Tensor,
-        key: torch.Tensor,
-        value: torch.Tensor,
-        key_cache: torch.Tensor,
-        value_cache: torch.Tensor,
-        block_tables: torch.Tensor,
-        query_start_loc: torch.Tensor,
-        seq_lens_tensor: torch.Tensor,
-        context_lens: torch.Tensor,
-        max_query_len: int,
-        alibi_slopes: Optional[torch.Tensor],
-        sliding_window: Optional[int],
-    ) -> torch.Tensor:
-        """paged_attn.py:185-216: prefill of new tokens against the cached prefix + themselves."""
-        output = torch.empty_like(query)
-        # same call as vllm_legacy_b200.attention.ops.prefix_prefill.context_attention_fwd
-        ops.context_attention_fwd(
-            query,
-            key,
-            value,
-            output,
-            key_cache,
-            value_cache,
-            block_tables,
-            # query_start_loc is (batch_size + 1,)
-            query_start_loc[:-1],
-            seq_lens_tensor,
-            context_lens,
-            max_query_len,
-            alibi_slopes,
-            sliding_window,
-        )
-        return output
+    def _pick_v1(num_seqs: int, num_heads: int, max_seq_len: int) -> bool:
+        """The reference's V1/V2 rule (paged_attn.py:112-121), same outcome for every input: V2 whenever the
+        context exceeds 8192 tokens; below that V1 if a single partition covers it or if the batch already has
+        more than 512 (sequence, head) pairs to fill the GPU."""
+        if max_seq_len > 8192:
+            return False
+        return PagedAttention._partitions(max_seq_len) == 1 or num_seqs * num_heads > 512
+
+    @staticmethod
+    def forward_decode(query: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                       block_tables: torch.Tensor, seq_lens: torch.Tensor, max_seq_len: int, kv_cache_dtype: str,
+                       num_kv_heads: int, scale: float, alibi_slopes: Optional[torch.Tensor], kv_scale: float,
+                       tp_rank: int = 0, blocksparse_local_blocks: int = 0, blocksparse_vert_stride: int = 0,
+                       blocksparse_block_size: int = 64, blocksparse_head_sliding_step: int = 0) -> torch.Tensor:
+        """One decode step over the paged cache (paged_attn.py:87-183): query [S, Hq, D] -> output [S, Hq, D]."""
+        num_seqs, num_heads, head_size = query.shape
+        block_size = value_cache.shape[3]
+        sparse = blocksparse_vert_stride is not None and blocksparse_vert_stride > 1
+        if sparse and not (blocksparse_block_size > 0 and blocksparse_block_size % block_size == 0):
+            raise AssertionError(f"{blocksparse_block_size=} needs to be a multiple of {block_size=} used in block_tables.")
+        tail = (num_kv_heads, scale, block_tables, seq_lens, block_size, max_seq_len, alibi_slopes, kv_cache_dtype,
+                kv_scale, tp_rank, blocksparse_local_blocks, blocksparse_vert_stride, blocksparse_block_size,
+                blocksparse_head_sliding_step)
+        out = torch.empty_like(query)
+        if PagedAttention._pick_v1(num_seqs, num_heads, max_seq_len):
+            ops.paged_attention_v1(out, query, key_cache, value_cache, *tail)
+            return out
+        assert _PARTITION_SIZE % block_size == 0
+        parts = PagedAttention._partitions(max_seq_len)
+        stats_shape = (num_seqs, num_heads, parts)
+        partial_out = torch.empty(size=(*stats_shape, head_size), dtype=out.dtype, device=out.device)
+        exp_sums = torch.empty(size=stats_shape, dtype=torch.float32, device=out.device)
+        max_logits = torch.empty_like(exp_sums)
+        ops.paged_attention_v2(out, exp_sums, max_logits, partial_out, query, key_cache, value_cache, *tail)
+        return out
+
+    @staticmethod
+    def forward_prefix(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor,
+                       value_cache: torch.Tensor, block_tables: torch.Tensor, query_start_loc: torch.Tensor,
+                       seq_lens_tensor: torch.Tensor, context_lens: torch.Tensor, max_query_len: int,
+                       alibi_slopes: Optional[torch.Tensor], sliding_window: Optional[int]) -> torch.Tensor:
+        """Prompt tokens against their cached prefix + themselves (paged_attn.py:185-216): one launch of the
+        sm_100a prefix-prefill kernel (csrc/prefill_tc.cu / prefill.cu).  `query_start_loc` has batch + 1 entries;
+        the kernel wants each sequence's first row, i.e. all but the last."""
+        out = torch.empty_like(query)
+        first_rows = query_start_loc[:-1]
+        ops.context_attention_fwd(query, key, value, out, key_cache, value_cache, block_tables, first_rows,
+                                  seq_lens_tensor, context_lens, max_query_len, alibi_slopes, sliding_window)
+        return out
 
     @staticmethod
     def swap_blocks(src_kv_cache: torch.Tensor, dst_kv_cache: torch.Tensor,

@@ -14,7 +14,7 @@
 // c10::BFloat16 operators, i.e. every product and every sum is evaluated in fp32 and rounded (RN-even)
 // back to the 16-bit type before the next operation (torch/headeronly/util/Half.h:501-511,
 // BFloat16.h:185-198).  For fp32 nvcc contracts the expressions to
-// fma(x, cos, -(y*sin)) and fma(y, cos, x*sin) (SASS of the reference build: FMUL; FMUL; FFMA; FFMA).
+// fma(x, cos, -(y*sin)) and fma(x, sin, y*cos) (SASS of the reference build: FMUL; FMUL; FFMA; FFMA).
 // Both forms are written out explicitly below with non-contractable intrinsics.
 #include <algorithm>
 
@@ -35,7 +35,7 @@ __device__ __forceinline__ void rotate_pair(T x, T y, T c, T s, T& nx, T& ny) {
 template <>
 __device__ __forceinline__ void rotate_pair<float>(float x, float y, float c, float s, float& nx, float& ny) {
   nx = __fmaf_rn(x, c, -__fmul_rn(y, s));
-  ny = __fmaf_rn(y, c, __fmul_rn(x, s));
+  ny = __fmaf_rn(x, s, __fmul_rn(y, c));
 }
 
 template <typename T, int VEC>
