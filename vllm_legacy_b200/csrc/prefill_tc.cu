@@ -72,6 +72,17 @@ __device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t a_desc, uint64_
       "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// D[tmem] (+)= A[tmem] . B[smem desc]: A = 128 lanes x (K/2) columns, each 32-bit cell two consecutive K elements
+__device__ __forceinline__ void tc_mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+      "}" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // 32 lanes x 32 consecutive 32-bit columns: thread i of the warp gets columns [c, c+32) of lane (base + i)
 __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
   asm volatile(
@@ -137,8 +148,8 @@ struct Geometry {
   static constexpr int QBYTES = kBM * DP * 2;  // [D/8][128 rows][16 B]
   static constexpr int KBYTES = kBN * DP * 2;  // [D/8][BN tokens][16 B]
   static constexpr int VBYTES = kBN * DP * 2;  // prefix: [BN/8][D rows][16 B]; new: [BN/8][D/8][8 tokens][16 B]
-  static constexpr int PBYTES = kBM * kBN * 2; // [BN/8][128 rows][16 B]
-  static constexpr int SMEM = QBYTES + 2 * KBYTES + 2 * VBYTES + PBYTES + 64;  // + barriers and the TMEM base slot
+  static constexpr int VSTAGES = 3;            // V(i) in use by PV(i), PV(i-1) possibly still running, V(i+1) landing
+  static constexpr int SMEM = QBYTES + 2 * KBYTES + VSTAGES * VBYTES + 64;  // + barriers and the TMEM base slot
   static constexpr int TMEM_COLS = 256;        // S0 [0,64) | S1 [64,128) | O [128, 128 + DP)
 };
 
@@ -191,10 +202,9 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
   const uint32_t q_smem = smem_u32(smem);
   const uint32_t k_smem = q_smem + G::QBYTES;
   const uint32_t v_smem = k_smem + 2 * G::KBYTES;
-  const uint32_t p_smem = v_smem + 2 * G::VBYTES;
-  const uint32_t bar_s = p_smem + G::PBYTES;  // two barriers (S0, S1); 8-byte aligned: region sizes are multiples of 128
-  const uint32_t bar_o = bar_s + 16;
-  constexpr int kSlotOff = G::QBYTES + 2 * G::KBYTES + 2 * G::VBYTES + G::PBYTES + 32;
+  const uint32_t bar_s = v_smem + G::VSTAGES * G::VBYTES;  // two barriers (S0, S1); region sizes are multiples of 128
+  const uint32_t bar_v = bar_s + 16;                       // one per V stage: "the PV that read this stage is done"
+  constexpr int kSlotOff = G::QBYTES + 2 * G::KBYTES + G::VSTAGES * G::VBYTES + 48;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kSlotOff);
 
   // ---- one-time setup: TMEM allocation (warp 0), mbarriers (thread 32) ----------------------------------
@@ -206,7 +216,7 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
   } else if (tid == 32) {
     mbar_init(bar_s, 1);
     mbar_init(bar_s + 8, 1);
-    mbar_init(bar_o, 1);
+    for (int s = 0; s < G::VSTAGES; ++s) mbar_init(bar_v + 8 * s, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
 
@@ -246,7 +256,7 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
   };
   auto load_v = [&](int it, int phys) {
     if (it >= n_tiles) return;
-    const uint32_t vb = v_smem + (it & 1) * G::VBYTES;
+    const uint32_t vb = v_smem + (it % G::VSTAGES) * G::VBYTES;
     if (it < n_ctx) {
       // (row d, 8 tokens starting at vg) -> (vg / 8) * (DP * 16) + d * 16     [K-major B operand, N = d]
       const int kpos = (c_first + it) * BN + vg;
@@ -321,7 +331,7 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
   for (int it = 0; it < n_tiles; ++it) {
     const bool is_ctx = it < n_ctx;
     const int t0 = is_ctx ? (c_first + it) * BN : (j_first + it - n_ctx) * BN;
-    const uint32_t vb = v_smem + (it & 1) * G::VBYTES;
+    const uint32_t vb = v_smem + (it % G::VSTAGES) * G::VBYTES;
 
     // ---- (a) K(it+1) and V(it) have landed ----------------------------------------------------------
     cp_async_wait<0>();
@@ -329,7 +339,7 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
       // last prefix tile: zero the V columns of tokens >= ctx_len (stale cache bits could be NaN; 0 * NaN = NaN)
       __syncthreads();
       const int nvalid = ctx_len - t0, cnt = BN - nvalid;
-      uint8_t* vrow = smem + G::QBYTES + 2 * G::KBYTES + (it & 1) * G::VBYTES;
+      uint8_t* vrow = smem + G::QBYTES + 2 * G::KBYTES + (it % G::VSTAGES) * G::VBYTES;
       for (int idx = tid; idx < DP * cnt; idx += kThreads) {
         const int d = idx / cnt, c = nvalid + (idx - d * cnt);
         *reinterpret_cast<uint16_t*>(vrow + (c >> 3) * (DP * 16) + d * 16 + (c & 7) * 2) = 0;
@@ -343,9 +353,9 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
       tc_fence_after();
       issue_qk(it + 1);
     }
-    // ---- (c, d) S(it) ready; PV(it-1) done: P, V(it-1)'s stage and O are ours again ------------------
+    // ---- (c, d) S(it) ready (K(it)'s stage is free); PV(it-2) done long ago (its V stage is free) --------
     mbar_wait(bar_s + 8 * (it & 1), (it >> 1) & 1);
-    if (it > 0) mbar_wait(bar_o, (it - 1) & 1);
+    if (it >= 2) mbar_wait(bar_v + 8 * ((it - 2) % G::VSTAGES), ((it - 2) / G::VSTAGES) & 1);
     tc_fence_after();
 
     // ---- (e) copies for the following iteration --------------------------------------------------------
@@ -400,6 +410,9 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
       m_ref = mx;
     }
     if (it > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
+      // the only place that needs PV(it-1) finished before the next PV is issued: O is about to be rewritten
+      mbar_wait(bar_v + 8 * ((it - 1) % G::VSTAGES), ((it - 1) / G::VSTAGES) & 1);
+      tc_fence_after();
 #pragma unroll 1
       for (int c0 = 0; c0 < DP; c0 += 32) {
         uint32_t o[32];
@@ -413,23 +426,20 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
     }
     float sum = 0.f;
     const float neg_ref = -m_ref;
+    // P (rounded to the 16-bit type) goes back into the TMEM columns its S row came from — two tokens per 32-bit
+    // cell — and is the A operand of the second MMA straight from Tensor Memory: no shared-memory round trip,
+    // and P is double buffered for free because S is.
+    uint32_t pw[BN / 2];
 #pragma unroll
-    for (int g = 0; g < BN / 8; ++g) {
-      uint32_t w[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float p0 = ex2(fmaf(__uint_as_float(sr[8 * g + 2 * j]), mult, neg_ref));
-        const float p1 = ex2(fmaf(__uint_as_float(sr[8 * g + 2 * j + 1]), mult, neg_ref));
-        sum += p0 + p1;
-        w[j] = pack2<T>(p0, p1);
-      }
-      // P (row tid, tokens 8g..8g+7) -> K-major A operand: g * (BM * 16) + row * 16
-      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(p_smem + g * (BM * 16) + tid * 16), "r"(w[0]),
-                   "r"(w[1]), "r"(w[2]), "r"(w[3])
-                   : "memory");
+    for (int c = 0; c < BN / 2; ++c) {
+      const float p0 = ex2(fmaf(__uint_as_float(sr[2 * c]), mult, neg_ref));
+      const float p1 = ex2(fmaf(__uint_as_float(sr[2 * c + 1]), mult, neg_ref));
+      sum += p0 + p1;
+      pw[c] = pack2<T>(p0, p1);
     }
+    tc_st32(tmem_base + (it & 1) * BN + lane_off, pw);
+    tc_wait_st();
     l_run = l_run * alpha + sum;
-    fence_proxy_async();
     tc_fence_before();
     __syncthreads();
 
@@ -438,14 +448,14 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
       tc_fence_after();
 #pragma unroll
       for (int kk = 0; kk < BN / 16; ++kk) {
-        const uint64_t a = make_desc(p_smem + kk * 2 * (BM * 16), BM * 16, 128);
         const uint64_t b = make_desc(vb + kk * 2 * (DP * 16), DP * 16, 128);
-        tc_mma(tmem_o, a, b, is_ctx ? idesc_pv_k : idesc_pv_mn, (it > 0 || kk > 0) ? 1u : 0u);
+        tc_mma_ts(tmem_o, tmem_base + (it & 1) * BN + kk * 8, b, is_ctx ? idesc_pv_k : idesc_pv_mn,
+                  (it > 0 || kk > 0) ? 1u : 0u);
       }
-      tc_commit(bar_o);
+      tc_commit(bar_v + 8 * (it % G::VSTAGES));
     }
   }
-  mbar_wait(bar_o, (n_tiles - 1) & 1);
+  mbar_wait(bar_v + 8 * ((n_tiles - 1) % G::VSTAGES), ((n_tiles - 1) / G::VSTAGES) & 1);
   tc_fence_after();
 
   // ---- epilogue: O / l -> out -------------------------------------------------------------------------
