@@ -166,3 +166,82 @@ def test_errors(ops):
         ops.context_attention_fwd(case["query"].cpu(), case["k"].cpu(), case["v"].cpu(), out.cpu(),
                                   case["k_cache"].cpu(), case["v_cache"].cpu(), case["block_table"].cpu(),
                                   case["b_start_loc"].cpu(), case["b_seq_len"].cpu(), case["b_ctx_len"].cpu(), 32)
+
+
+@pytest.mark.parametrize("seed", range(24))
+@torch.inference_mode()
+def test_random_ragged_batches(ops, seed):
+    """Randomised shapes over both kernel families: ragged query/context lengths (including 0-token prefixes and
+    1-token queries), GQA ratios, head sizes, block sizes, windows, ALiBi."""
+    import random
+    rng = random.Random(1000 + seed)
+    dtype = rng.choice([torch.float16, torch.bfloat16])
+    head_size = rng.choice([64, 128, 128, 128, 80, 96, 256])
+    qpk = rng.choice([1, 2, 4, 8])
+    num_heads = qpk * rng.choice([1, 2, 3])
+    block_size = rng.choice([8, 16, 16, 32, 64])
+    batch = rng.randint(1, 6)
+    qmax = rng.choice([1, 17, 64, 65, 129, 400, 700])
+    query_lens = [rng.randint(1, qmax) for _ in range(batch)]
+    ctx_lens = [rng.choice([0, rng.randint(1, 900)]) for _ in range(batch)]
+    mode = rng.choice(["plain", "plain", "window", "alibi"])
+    case = helpers.make_prefill_case(num_heads, qpk, head_size, dtype, DEV, query_lens=query_lens, ctx_lens=ctx_lens,
+                                     block_size=block_size, amplitude=1.0, seed=seed, stale_nan=True)
+    slopes = _alibi_slopes(num_heads).to(DEV) if mode == "alibi" else None
+    window = rng.choice([1, 7, 64, 130, 1000]) if mode == "window" else 0
+    out = _run(ops, case, slopes, window)
+    ref = helpers.ref_context_attention(case, slopes, window)
+    assert not torch.isnan(out).any()
+    atol = 1e-3 if dtype == torch.float16 else 4e-3
+    torch.testing.assert_close(out.float(), ref, atol=atol, rtol=1e-2)
+
+
+@torch.inference_mode()
+def test_deterministic_and_graph_capturable(ops):
+    """Same inputs -> bit-identical output on every launch; the op allocates nothing and never synchronises when the
+    index tensors are int32, so a prefill chunk can be captured in a CUDA graph and replayed."""
+    case = helpers.make_prefill_case(16, 4, 128, torch.bfloat16, DEV, batch=4, max_q=300, max_ctx=500, amplitude=1.0,
+                                     block_size=16)
+    a = _run(ops, case)
+    b = _run(ops, case)
+    assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+    out = torch.zeros_like(case["query"])
+    args = (case["query"], case["k"], case["v"], out, case["k_cache"], case["v_cache"], case["block_table"],
+            case["b_start_loc"], case["b_seq_len"], case["b_ctx_len"], case["max_input_len"], None, 0)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        ops.context_attention_fwd(*args)
+    torch.cuda.current_stream().wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        ops.context_attention_fwd(*args)
+    out.zero_()
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out.view(torch.int16), a.view(torch.int16))
+
+
+@torch.inference_mode()
+def test_long_context_chunk(ops):
+    """BASELINE-sized shape through a size-independent property: a 512-token chunk over a 32k-token prefix with
+    constant V must return that constant for every row and head (softmax weights sum to 1), and permuting the
+    physical blocks must not change a bit."""
+    H, qpk, D, B = 8, 4, 128, 16
+    case = helpers.make_prefill_case(H, qpk, D, torch.bfloat16, DEV, query_lens=[512], ctx_lens=[32768], block_size=B,
+                                     amplitude=1.0)
+    a = _run(ops, case)
+    perm = torch.randperm(case["k_cache"].shape[0], device=DEV)
+    inv = torch.empty_like(perm)
+    inv[perm] = torch.arange(perm.numel(), device=DEV)
+    case2 = dict(case)
+    case2["k_cache"] = case["k_cache"][perm].contiguous()
+    case2["v_cache"] = case["v_cache"][perm].contiguous()
+    case2["block_table"] = inv[case["block_table"].long()].to(torch.int32)
+    b = _run(ops, case2)
+    assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+    case3 = dict(case)
+    case3["v_cache"] = torch.full_like(case["v_cache"], 0.5)
+    case3["v"] = torch.full_like(case["v"], 0.5)
+    c = _run(ops, case3)
+    torch.testing.assert_close(c.float(), torch.full_like(c, 0.5).float(), atol=4e-3, rtol=0)
