@@ -1,20 +1,27 @@
-// context_attention_fwd on the 5th-generation tensor cores (sm_100a): tcgen05.mma with the S and O accumulators
-// in Tensor Memory.  Same contract as prefill.cu (which stays the family for shapes this file does not
-// instantiate); replaces vllm/attention/ops/prefix_prefill.py:10-245, 442-681.
+// context_attention_fwd on the 5th-generation tensor cores (sm_100a): tcgen05.mma with the S, P and O operands in
+// Tensor Memory.  Same contract as prefill.cu (which stays the family for shapes this file does not instantiate);
+// replaces vllm/attention/ops/prefix_prefill.py:10-245, 442-681.
 //
-//   * one CTA = 128 query rows of one (sequence, query head) = the UMMA M; 128 threads, thread t owns row t
-//     (TMEM lane t), so softmax row reductions are thread-local — no shuffles;
-//   * S[128 x BN] = Q K^T : D/16 tcgen05.mma (M128 N64 K16, kind::f16, fp32 accumulate) issued by ONE thread,
+//   * one CTA = 128 query rows of one (sequence, query head) = the UMMA M; softmax thread t owns row t (TMEM lane t),
+//     so row maxima and sums are thread-local — no shuffles;
+//   * S[128 x 64] = Q K^T : D/16 tcgen05.mma (M128 N64 K16, kind::f16, fp32 accumulate) issued by ONE thread,
 //     A = Q tile and B = K tile in shared memory in the canonical no-swizzle K-major core-matrix layout
 //     (8 rows x 16 B contiguous) — the paged K chunk [D/8][B][8] already IS that layout per block, the staging
 //     copy only re-bases the 8-token groups of several blocks to one uniform stride;
-//   * softmax: tcgen05.ld the row (32x32b), exp2 in registers, P rounded to the 16-bit type and stored to shared
-//     memory as the K-major A operand of the second MMA; the running maximum is only advanced when it grows by
-//     more than 2^8 (the O accumulator in TMEM is then rescaled through tcgen05.ld/st), so the rescale is rare;
-//   * O[128 x D] += P V : BN/16 tcgen05.mma, B = V tile K-major for the cached prefix (the paged V chunk
-//     [D][B] is token-minor) and MN-major for the new tokens ([token][d] rows) — no transposition anywhere;
-//   * K/V tiles are staged with 16-byte cp.async straight into the core-matrix layouts, double buffered; the MMAs
-//     complete on mbarriers via tcgen05.commit; two CTAs per SM overlap one CTA's softmax with the other's MMAs.
+//   * softmax: tcgen05.ld the row (32x32b), p = 2^(s * scale * log2e - m_ref) with one FFMA + MUFU per element, P
+//     rounded to the 16-bit type and written with tcgen05.st OVER ITS OWN S COLUMNS (two tokens per 32-bit cell):
+//     the second MMA reads its A operand straight from Tensor Memory.  The reference maximum m_ref is lazy: it only
+//     moves when the row maximum grows by more than 2^8, so O (in TMEM) is rescaled a few times per row at most;
+//   * O[128 x D] += P V : 4 tcgen05.mma, B = V tile K-major for the cached prefix (the paged V chunk [D][B] is
+//     token-minor) and MN-major for the new tokens ([token][d] rows) — nothing is ever transposed;
+//   * K/V tiles are staged with 16-byte cp.async straight into the core-matrix layouts (tokens behind ctx_len are
+//     zero-filled by the copy's src-size); MMA completion is signalled with tcgen05.commit -> mbarrier.
+//
+// Two kernels share these pieces:
+//   context_attention_ws_kernel (default)  warp-specialised: 4 softmax warps + 1 warp that stages Q/K and issues
+//                                          every MMA; the roles only meet on mbarriers, no __syncthreads in the loop;
+//   context_attention_tc_kernel            the same pipeline with all four warps doing everything (two CTA-wide
+//                                          barriers per tile); kept selectable with B200PA_PREFILL_WS=0.
 #include <cstdlib>
 #include <type_traits>
 
@@ -489,6 +496,385 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
   }
 }
 
+// ====================================================================================================
+// Warp-specialised variant: warps 0-3 do nothing but softmax (thread t = query row t = TMEM lane t), warp 4
+// stages K/V (all 32 lanes, 16-byte cp.async into the core-matrix layouts) and issues every MMA (lane 0).
+// The roles meet only on mbarriers:
+//   s_full[2]  : S(i) = Q K(i)^T finished                      (tcgen05.commit)     softmax waits, producer waits (K stage free)
+//   p_full[2]  : all 128 softmax threads stored P(i) to TMEM   (128 arrivals)       producer waits before issuing P(i) V(i)
+//   pv_done[3] : P(i) V(i) finished, per V stage               (tcgen05.commit)     producer waits (V stage free); softmax waits
+//                                                                                    only before rescaling O and in the epilogue
+// No __syncthreads in the main loop.  Tensor-pipe order: QK(0), QK(1), PV(0), QK(2), PV(1), ... so the next S is
+// always being computed while the softmax warps work on the current one.
+// ====================================================================================================
+constexpr int kWsThreads = 160;
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+template <typename T, int DP>
+__global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(const __grid_constant__ PrefillParams p) {
+  using G = Geometry<DP>;
+  constexpr int BM = kBM, BN = kBN;
+  constexpr int DG = DP / 8;
+  extern __shared__ __align__(128) uint8_t smem[];
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+
+  const int head = blockIdx.x;
+  const int mt_idx = gridDim.y - 1 - blockIdx.y;
+  const int seq = blockIdx.z;
+  const int ctx_len = p.ctx_lens[seq];
+  const int q_len = p.seq_lens[seq] - ctx_len;
+  const int m0 = mt_idx * BM;
+  if (m0 >= q_len) return;
+  const int64_t tok0 = p.start_loc[seq];
+  const int kv_head = head / (p.num_heads / p.num_kv_heads);
+  const int D = p.head_size;
+  const int W = p.alibi_slopes ? 0 : p.sliding_window;
+  const int bshift = p.block_shift;
+  const int B = 1 << bshift;
+
+  int c_first = 0, j_first = 0;
+  if (W > 0) {
+    c_first = max(0, ctx_len + m0 - W + 1) / BN;
+    j_first = max(0, m0 - W + 1) / BN;
+  }
+  const int c_end = (ctx_len + BN - 1) / BN;
+  const int j_end = (min(q_len, m0 + BM) + BN - 1) / BN;
+  const int n_ctx = max(0, c_end - c_first);
+  const int n_tiles = n_ctx + (j_end - j_first);
+
+  const uint32_t q_smem = smem_u32(smem);
+  const uint32_t k_smem = q_smem + G::QBYTES;
+  const uint32_t v_smem = k_smem + 2 * G::KBYTES;
+  const uint32_t bars = v_smem + G::VSTAGES * G::VBYTES;
+  const uint32_t s_full = bars, p_full = bars + 16, pv_done = bars + 32;  // 2 + 2 + 3 barriers of 8 bytes
+  constexpr int kSlotOff = G::QBYTES + 2 * G::KBYTES + G::VSTAGES * G::VBYTES + 56;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kSlotOff);
+
+  if (warp == 4) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "n"(G::TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  } else if (tid == 0) {
+    mbar_init(s_full, 1);
+    mbar_init(s_full + 8, 1);
+    mbar_init(p_full, 128);
+    mbar_init(p_full + 8, 128);
+    for (int s = 0; s < G::VSTAGES; ++s) mbar_init(pv_done + 8 * s, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_o = tmem_base + 2 * BN;
+
+  if (warp == 4) {
+    // ================================ producer + MMA issuer ================================
+    const T* kc = static_cast<const T*>(p.k_cache) + (int64_t)kv_head * p.kc_head_stride;
+    const T* vc = static_cast<const T*>(p.v_cache) + (int64_t)kv_head * p.vc_head_stride;
+    const T* kn = static_cast<const T*>(p.k) + tok0 * p.k_stride_t + (int64_t)kv_head * p.k_stride_h;
+    const T* vn = static_cast<const T*>(p.v) + tok0 * p.v_stride_t + (int64_t)kv_head * p.v_stride_h;
+    const int* table = p.block_tables + (int64_t)seq * p.block_table_stride;
+
+    // lane l copies tokens l and l + 32 of a K / new-V tile and the 8-token group l % 8 of a cached V tile, so it
+    // needs three block-table entries per tile; they are fetched one refill ahead (ek0 / ek1 / ev) so that no
+    // copy ever waits on a dependent global load.
+    auto k_entry = [&](int it, int h) -> int {
+      const int kpos = (c_first + it) * BN + lane + 32 * h;
+      return (it < n_ctx && kpos < ctx_len) ? table[kpos >> bshift] : -1;
+    };
+    auto load_k = [&](int it, int e0, int e1) {
+      if (it >= n_tiles) return;
+      const uint32_t kb = k_smem + (it & 1) * G::KBYTES;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int kt = lane + 32 * h;
+        const uint32_t dst = kb + kt * 16;  // (token t, d-group g) -> g * (BN * 16) + t * 16
+        if (it < n_ctx) {
+          const int phys = h ? e1 : e0;
+          const int kpos = (c_first + it) * BN + kt;
+          const T* src = kc + (int64_t)max(phys, 0) * p.kc_block_stride + (kpos & (B - 1)) * 8;
+#pragma unroll
+          for (int g = 0; g < DG; ++g) {
+            const bool ok = phys >= 0 && g * 8 < D;
+            cp_async16(dst + g * (BN * 16), ok ? (const void*)(src + (int64_t)g * B * 8) : (const void*)kc, ok ? 16 : 0);
+          }
+        } else {
+          const int j = (j_first + it - n_ctx) * BN + kt;
+          const T* src = kn + (int64_t)j * p.k_stride_t;
+#pragma unroll
+          for (int g = 0; g < DG; ++g) {
+            const bool ok = j < q_len && g * 8 < D;
+            cp_async16(dst + g * (BN * 16), ok ? (const void*)(src + g * 8) : (const void*)kn, ok ? 16 : 0);
+          }
+        }
+      }
+    };
+    {  // Q: rows lane, lane + 32, lane + 64, lane + 96
+      const T* qb = static_cast<const T*>(p.q) + tok0 * p.q_stride_t + (int64_t)head * p.q_stride_h;
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        const int r = lane + 32 * h;
+        const bool rv = m0 + r < q_len;
+        const T* src = qb + (int64_t)(m0 + r) * p.q_stride_t;
+#pragma unroll
+        for (int c = 0; c < DG; ++c) {
+          const bool ok = rv && c * 8 < D;
+          cp_async16(q_smem + c * (BM * 16) + r * 16, ok ? (const void*)(src + c * 8) : (const void*)qb, ok ? 16 : 0);
+        }
+      }
+    }
+    load_k(0, k_entry(0, 0), k_entry(0, 1));
+    cp_async_commit();  // G: Q, K(0)
+    load_k(1, k_entry(1, 0), k_entry(1, 1));
+    cp_async_commit();  // G: K(1)
+    int ek0 = k_entry(2, 0), ek1 = k_entry(2, 1);  // for the refill of iteration 0
+
+    constexpr uint32_t idesc_qk = make_idesc<T>(BM, BN, 0);
+    constexpr uint32_t idesc_pv_k = make_idesc<T>(BM, DP, 0);
+    constexpr uint32_t idesc_pv_mn = make_idesc<T>(BM, DP, 1);
+    auto issue_qk = [&](int it) {
+      const uint32_t kb = k_smem + (it & 1) * G::KBYTES;
+#pragma unroll
+      for (int ks = 0; ks < DP / 16; ++ks) {
+        const uint64_t a = make_desc(q_smem + ks * 2 * (BM * 16), BM * 16, 128);
+        const uint64_t b = make_desc(kb + ks * 2 * (BN * 16), BN * 16, 128);
+        tc_mma(tmem_base + (it & 1) * BN, a, b, idesc_qk, ks > 0 ? 1u : 0u);
+      }
+      tc_commit(s_full + 8 * (it & 1));
+    };
+
+    cp_async_wait<1>();  // Q, K(0)
+    fence_proxy_async();
+    __syncwarp();
+    if (lane == 0) issue_qk(0);
+
+    for (int it = 0; it < n_tiles; ++it) {
+      cp_async_wait<0>();  // K(it+1) has landed (this lane's part; the fence + syncwarp cover the warp)
+      const bool is_ctx = it < n_ctx;
+      const uint32_t vb = v_smem + (it % G::VSTAGES) * G::VBYTES;
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0 && it + 1 < n_tiles) {
+        tc_fence_after();
+        issue_qk(it + 1);
+      }
+      // refill K(it+2) once QK(it) has finished with its stage (the softmax warps stage V, see below)
+      if (it + 2 < n_tiles) {
+        mbar_wait(s_full + 8 * (it & 1), (it >> 1) & 1);
+        load_k(it + 2, ek0, ek1);
+      }
+      cp_async_commit();
+      ek0 = k_entry(it + 3, 0);
+      ek1 = k_entry(it + 3, 1);
+      // P(it) is in TMEM and every softmax thread's share of V(it) has landed: O += P(it) V(it)
+      mbar_wait(p_full + 8 * (it & 1), (it >> 1) & 1);
+      tc_fence_after();
+      if (lane == 0) {
+#pragma unroll
+        for (int kk = 0; kk < BN / 16; ++kk) {
+          const uint64_t b = make_desc(vb + kk * 2 * (DP * 16), DP * 16, 128);
+          tc_mma_ts(tmem_o, tmem_base + (it & 1) * BN + kk * 8, b, is_ctx ? idesc_pv_k : idesc_pv_mn,
+                    (it > 0 || kk > 0) ? 1u : 0u);
+        }
+        tc_commit(pv_done + 8 * (it % G::VSTAGES));
+      }
+      __syncwarp();
+    }
+    cp_async_wait<0>();
+  } else {
+    // ================================ softmax warps: thread = query row ================================
+    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+    const float slope_l2 = p.alibi_slopes ? p.alibi_slopes[head] * kLog2e : 0.f;
+    const bool has_alibi = p.alibi_slopes != nullptr;
+    const int m = m0 + tid;
+    float m_ref = kNegBig, l_run = 0.f;
+
+    // The 128 softmax threads also stage V (8 sixteen-byte copies each per tile, issued right after their P is
+    // stored): thread t always copies the 8-token group t % 8 (cached V) or token t % 64 (new V), so it needs one
+    // block-table entry per tile, fetched a tile ahead.  Tokens >= ctx_len inside the last group are zero-filled
+    // by the copy itself (src-size < 16), so stale NaN bits behind the prefix never reach the tensor core.
+    const T* vc = static_cast<const T*>(p.v_cache) + (int64_t)kv_head * p.vc_head_stride;
+    const T* vn = static_cast<const T*>(p.v) + tok0 * p.v_stride_t + (int64_t)kv_head * p.v_stride_h;
+    const int* table = p.block_tables + (int64_t)seq * p.block_table_stride;
+    const int vg = (tid & 7) * 8;
+    const int kt = tid % BN;
+    auto v_entry = [&](int it) -> int {
+      const int kpos = (c_first + it) * BN + vg;
+      return (it < n_ctx && kpos < ctx_len) ? table[kpos >> bshift] : -1;
+    };
+    auto load_v = [&](int it, int phys) {
+      if (it >= n_tiles) return;
+      const uint32_t vb = v_smem + (it % G::VSTAGES) * G::VBYTES;
+      if (it < n_ctx) {
+        const int kpos = (c_first + it) * BN + vg;
+        const int nbytes = 2 * min(8, max(0, ctx_len - kpos));
+        const T* src = vc + (int64_t)max(phys, 0) * p.vc_block_stride + (kpos & (B - 1));
+        const uint32_t dst = vb + (vg >> 3) * (DP * 16);  // (row d, 8 tokens at vg) -> (vg / 8) * (DP * 16) + d * 16
+#pragma unroll
+        for (int d = tid >> 3; d < DP; d += 16) {
+          const bool ok = phys >= 0 && d < D;
+          cp_async16(dst + d * 16, ok ? (const void*)(src + (int64_t)d * B) : (const void*)vc, ok ? nbytes : 0);
+        }
+      } else {
+        const int j = (j_first + it - n_ctx) * BN + kt;
+        const T* src = vn + (int64_t)j * p.v_stride_t;
+        const uint32_t dst = vb + (kt >> 3) * (DP * 16) + (kt & 7) * 16;  // MN-major core matrices
+#pragma unroll
+        for (int g = tid / BN; g < DG; g += 2) {
+          const bool ok = j < q_len && g * 8 < D;
+          cp_async16(dst + g * 128, ok ? (const void*)(src + g * 8) : (const void*)vn, ok ? 16 : 0);
+        }
+      }
+    };
+    load_v(0, v_entry(0));
+    cp_async_commit();
+    load_v(1, v_entry(1));
+    cp_async_commit();
+    int ev = v_entry(2);
+
+    for (int it = 0; it < n_tiles; ++it) {
+      const bool is_ctx = it < n_ctx;
+      const int t0 = is_ctx ? (c_first + it) * BN : (j_first + it - n_ctx) * BN;
+      mbar_wait(s_full + 8 * (it & 1), (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t ts = tmem_base + (it & 1) * BN + lane_off;
+      uint32_t sr[BN];
+      {
+        uint32_t (&lo)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sr[0]);
+        uint32_t (&hi)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sr[32]);
+        tc_ld32(ts, lo);
+        tc_ld32(ts + 32, hi);
+        tc_wait_ld();
+      }
+      const int base_rel = is_ctx ? (t0 - ctx_len) : t0;
+      const int col_limit = is_ctx ? (ctx_len - t0) : BN;
+      bool need_mask;
+      if (is_ctx)
+        need_mask = (t0 + BN > ctx_len) || (W > 0 && ctx_len + m0 + BM - 1 - t0 >= W);
+      else
+        need_mask = (t0 + BN - 1 > m0) || (W > 0 && m0 + BM - 1 - t0 >= W);
+      float mx = kNegBig;
+      float mult;  // p = 2^(sr * mult - m_ref)
+      if (need_mask || has_alibi) {
+#pragma unroll
+        for (int c = 0; c < BN; ++c) {
+          const int rel = base_rel + c - m;
+          float z = __uint_as_float(sr[c]) * p.scale_log2;
+          if (has_alibi) z = fmaf(slope_l2, (float)rel, z);
+          const bool vis = !need_mask || (c < col_limit && rel <= 0 && (W <= 0 || -rel < W));
+          z = vis ? z : kNegBig;
+          sr[c] = __float_as_uint(z);
+          mx = fmaxf(mx, z);
+        }
+        mult = 1.f;
+      } else {
+#pragma unroll
+        for (int c = 0; c < BN; ++c) mx = fmaxf(mx, __uint_as_float(sr[c]));
+        mx *= p.scale_log2;
+        mult = p.scale_log2;
+      }
+      float alpha = 1.f;
+      if (mx > m_ref + 8.f) {  // lazy reference maximum (see the kernel above)
+        alpha = ex2(m_ref - mx);
+        m_ref = mx;
+      }
+      if (it > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
+        mbar_wait(pv_done + 8 * ((it - 1) % G::VSTAGES), ((it - 1) / G::VSTAGES) & 1);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c0 = 0; c0 < DP; c0 += 32) {
+          uint32_t o[32];
+          tc_ld32(tmem_o + lane_off + c0, o);
+          tc_wait_ld();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * alpha);
+          tc_st32(tmem_o + lane_off + c0, o);
+        }
+        tc_wait_st();
+      }
+      float sum = 0.f;
+      const float neg_ref = -m_ref;
+      uint32_t pw[BN / 2];
+#pragma unroll
+      for (int c = 0; c < BN / 2; ++c) {
+        const float p0 = ex2(fmaf(__uint_as_float(sr[2 * c]), mult, neg_ref));
+        const float p1 = ex2(fmaf(__uint_as_float(sr[2 * c + 1]), mult, neg_ref));
+        sum += p0 + p1;
+        pw[c] = pack2<T>(p0, p1);
+      }
+      tc_st32(ts, pw);  // P over its own S columns: the A operand of P.V, read from Tensor Memory
+      tc_wait_st();
+      l_run = l_run * alpha + sum;
+      // V(it+2) into the stage PV(it-1) has long finished with; then make sure this thread's share of V(it) landed
+      if (it + 2 < n_tiles) {
+        if (it >= 1) mbar_wait(pv_done + 8 * ((it - 1) % G::VSTAGES), ((it - 1) / G::VSTAGES) & 1);
+        load_v(it + 2, ev);
+      }
+      cp_async_commit();
+      ev = v_entry(it + 3);
+      cp_async_wait<2>();
+      fence_proxy_async();
+      tc_fence_before();
+      mbar_arrive(p_full + 8 * (it & 1));
+    }
+    mbar_wait(pv_done + 8 * ((n_tiles - 1) % G::VSTAGES), ((n_tiles - 1) / G::VSTAGES) & 1);
+    tc_fence_after();
+    {
+      const float inv = 1.f / l_run;
+      T* orow = static_cast<T*>(p.out) + (tok0 + m) * p.o_stride_t + (int64_t)head * p.o_stride_h;
+#pragma unroll 1
+      for (int c0 = 0; c0 < DP; c0 += 32) {
+        uint32_t o[32];
+        tc_ld32(tmem_o + lane_off + c0, o);
+        tc_wait_ld();
+        if (m < q_len) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            if (c0 + j < D) {
+              uint4 w;
+              w.x = pack2<T>(__uint_as_float(o[j]) * inv, __uint_as_float(o[j + 1]) * inv);
+              w.y = pack2<T>(__uint_as_float(o[j + 2]) * inv, __uint_as_float(o[j + 3]) * inv);
+              w.z = pack2<T>(__uint_as_float(o[j + 4]) * inv, __uint_as_float(o[j + 5]) * inv);
+              w.w = pack2<T>(__uint_as_float(o[j + 6]) * inv, __uint_as_float(o[j + 7]) * inv);
+              *reinterpret_cast<uint4*>(orow + c0 + j) = w;
+            }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(G::TMEM_COLS) : "memory");
+  }
+}
+
+template <typename T, int DP>
+static int launch_ws(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
+  using G = Geometry<DP>;
+  auto kernel = context_attention_ws_kernel<T, DP>;
+  static bool configured[64] = {false};
+  int dev = 0;
+  B200PA_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    B200PA_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM + 64));
+    if (dev >= 0 && dev < 64) configured[dev] = true;
+  }
+  dim3 grid(kp.num_heads, (max_query_len + kBM - 1) / kBM, batch);
+  kernel<<<grid, kWsThreads, G::SMEM + 64, stream>>>(kp);
+  B200PA_CUDA_CHECK(cudaGetLastError());
+  return B200PA_OK;
+}
+
 template <typename T, int DP>
 static int launch(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
   using G = Geometry<DP>;
@@ -508,12 +894,25 @@ static int launch(const PrefillParams& kp, int batch, int max_query_len, cudaStr
 
 }  // namespace prefill_tc
 
+static constexpr int kWsDefault = 1;
+
 int launch_prefill_tc(const PrefillParams& kp, int batch, int max_query_len, int dtype, cudaStream_t stream) {
   auto mis16 = [](const void* ptr) { return reinterpret_cast<uintptr_t>(ptr) % 16 != 0; };
   // 16-byte rows for the cp.async of Q and the 128-bit stores of O
   if (mis16(kp.q) || mis16(kp.out) || kp.q_stride_t % 8 || kp.q_stride_h % 8 || kp.o_stride_t % 8 || kp.o_stride_h % 8) return 1;
   const int d = kp.head_size;
   if (d % 16 != 0) return 1;
+  static const int ws_knob = [] { const char* e = std::getenv("B200PA_PREFILL_WS"); return e ? std::atoi(e) : kWsDefault; }();
+  if (ws_knob) {
+    if (dtype == B200PA_F16) {
+      if (d <= 64) return prefill_tc::launch_ws<__half, 64>(kp, batch, max_query_len, stream);
+      if (d <= 128) return prefill_tc::launch_ws<__half, 128>(kp, batch, max_query_len, stream);
+    } else if (dtype == B200PA_BF16) {
+      if (d <= 64) return prefill_tc::launch_ws<__nv_bfloat16, 64>(kp, batch, max_query_len, stream);
+      if (d <= 128) return prefill_tc::launch_ws<__nv_bfloat16, 128>(kp, batch, max_query_len, stream);
+    }
+    return 1;
+  }
   if (dtype == B200PA_F16) {
     if (d <= 64) return prefill_tc::launch<__half, 64>(kp, batch, max_query_len, stream);
     if (d <= 128) return prefill_tc::launch<__half, 128>(kp, batch, max_query_len, stream);
