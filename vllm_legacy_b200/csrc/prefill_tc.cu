@@ -19,7 +19,7 @@
 //
 // Two kernels share these pieces:
 //   context_attention_ws_kernel (default)  warp-specialised: 4 softmax warps + 1 warp that stages Q/K and issues
-//                                          every MMA; the roles only meet on mbarriers, no __syncthreads in the loop;
+//                                          every MMA + 1 warp that stages V; the roles only meet on mbarriers;
 //   context_attention_tc_kernel            the same pipeline with all four warps doing everything (two CTA-wide
 //                                          barriers per tile); kept selectable with B200PA_PREFILL_WS=0.
 #include <cstdlib>
@@ -507,7 +507,7 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
 // No __syncthreads in the main loop.  Tensor-pipe order: QK(0), QK(1), PV(0), QK(2), PV(1), ... so the next S is
 // always being computed while the softmax warps work on the current one.
 // ====================================================================================================
-constexpr int kWsThreads = 160;
+constexpr int kWsThreads = 192;
 
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
@@ -552,8 +552,8 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
   const uint32_t k_smem = q_smem + G::QBYTES;
   const uint32_t v_smem = k_smem + 2 * G::KBYTES;
   const uint32_t bars = v_smem + G::VSTAGES * G::VBYTES;
-  const uint32_t s_full = bars, p_full = bars + 16, pv_done = bars + 32;  // 2 + 2 + 3 barriers of 8 bytes
-  constexpr int kSlotOff = G::QBYTES + 2 * G::KBYTES + G::VSTAGES * G::VBYTES + 56;
+  const uint32_t s_full = bars, p_full = bars + 16, pv_done = bars + 32, v_full = bars + 56;  // 2 + 2 + 3 + 3 barriers
+  constexpr int kSlotOff = G::QBYTES + 2 * G::KBYTES + G::VSTAGES * G::VBYTES + 96;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kSlotOff);
 
   if (warp == 4) {
@@ -567,6 +567,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
     mbar_init(p_full, 128);
     mbar_init(p_full + 8, 128);
     for (int s = 0; s < G::VSTAGES; ++s) mbar_init(pv_done + 8 * s, 1);
+    for (int s = 0; s < G::VSTAGES; ++s) mbar_init(v_full + 8 * s, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   tc_fence_before();
@@ -674,7 +675,8 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
       cp_async_commit();
       ek0 = k_entry(it + 3, 0);
       ek1 = k_entry(it + 3, 1);
-      // P(it) is in TMEM and every softmax thread's share of V(it) has landed: O += P(it) V(it)
+      // V(it) has landed (warp 5) and P(it) is in TMEM (softmax warps): O += P(it) V(it)
+      mbar_wait(v_full + 8 * (it % G::VSTAGES), (it / G::VSTAGES) & 1);
       mbar_wait(p_full + 8 * (it & 1), (it >> 1) & 1);
       tc_fence_after();
       if (lane == 0) {
@@ -689,23 +691,16 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
       __syncwarp();
     }
     cp_async_wait<0>();
-  } else {
-    // ================================ softmax warps: thread = query row ================================
-    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
-    const float slope_l2 = p.alibi_slopes ? p.alibi_slopes[head] * kLog2e : 0.f;
-    const bool has_alibi = p.alibi_slopes != nullptr;
-    const int m = m0 + tid;
-    float m_ref = kNegBig, l_run = 0.f;
-
-    // The 128 softmax threads also stage V (8 sixteen-byte copies each per tile, issued right after their P is
-    // stored): thread t always copies the 8-token group t % 8 (cached V) or token t % 64 (new V), so it needs one
-    // block-table entry per tile, fetched a tile ahead.  Tokens >= ctx_len inside the last group are zero-filled
-    // by the copy itself (src-size < 16), so stale NaN bits behind the prefix never reach the tensor core.
+  } else if (warp == 5) {
+    // ================================ V loader ================================
+    // Lane l always copies the 8-token group l % 8 (cached V: rows l / 8, l / 8 + 4, ...) or tokens l and l + 32
+    // (new V), so it needs one block-table entry per tile, fetched a tile ahead.  Tokens >= ctx_len inside the last
+    // group are zero-filled by the copy itself (src-size < 16): stale NaN bits behind the prefix never reach the
+    // tensor core.
     const T* vc = static_cast<const T*>(p.v_cache) + (int64_t)kv_head * p.vc_head_stride;
     const T* vn = static_cast<const T*>(p.v) + tok0 * p.v_stride_t + (int64_t)kv_head * p.v_stride_h;
     const int* table = p.block_tables + (int64_t)seq * p.block_table_stride;
-    const int vg = (tid & 7) * 8;
-    const int kt = tid % BN;
+    const int vg = (lane & 7) * 8;
     auto v_entry = [&](int it) -> int {
       const int kpos = (c_first + it) * BN + vg;
       return (it < n_ctx && kpos < ctx_len) ? table[kpos >> bshift] : -1;
@@ -718,19 +713,23 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
         const int nbytes = 2 * min(8, max(0, ctx_len - kpos));
         const T* src = vc + (int64_t)max(phys, 0) * p.vc_block_stride + (kpos & (B - 1));
         const uint32_t dst = vb + (vg >> 3) * (DP * 16);  // (row d, 8 tokens at vg) -> (vg / 8) * (DP * 16) + d * 16
-#pragma unroll
-        for (int d = tid >> 3; d < DP; d += 16) {
+#pragma unroll 8
+        for (int d = lane >> 3; d < DP; d += 4) {
           const bool ok = phys >= 0 && d < D;
           cp_async16(dst + d * 16, ok ? (const void*)(src + (int64_t)d * B) : (const void*)vc, ok ? nbytes : 0);
         }
       } else {
-        const int j = (j_first + it - n_ctx) * BN + kt;
-        const T* src = vn + (int64_t)j * p.v_stride_t;
-        const uint32_t dst = vb + (kt >> 3) * (DP * 16) + (kt & 7) * 16;  // MN-major core matrices
 #pragma unroll
-        for (int g = tid / BN; g < DG; g += 2) {
-          const bool ok = j < q_len && g * 8 < D;
-          cp_async16(dst + g * 128, ok ? (const void*)(src + g * 8) : (const void*)vn, ok ? 16 : 0);
+        for (int h = 0; h < 2; ++h) {
+          const int kt = lane + 32 * h;
+          const int j = (j_first + it - n_ctx) * BN + kt;
+          const T* src = vn + (int64_t)j * p.v_stride_t;
+          const uint32_t dst = vb + (kt >> 3) * (DP * 16) + (kt & 7) * 16;  // MN-major core matrices
+#pragma unroll
+          for (int g = 0; g < DG; ++g) {
+            const bool ok = j < q_len && g * 8 < D;
+            cp_async16(dst + g * 128, ok ? (const void*)(src + g * 8) : (const void*)vn, ok ? 16 : 0);
+          }
         }
       }
     };
@@ -739,6 +738,27 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
     load_v(1, v_entry(1));
     cp_async_commit();
     int ev = v_entry(2);
+    for (int it = 0; it < n_tiles; ++it) {
+      cp_async_wait<1>();  // V(it) landed (this lane's share)
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(v_full + 8 * (it % G::VSTAGES));
+      // V(it+2) goes into the stage PV(it-1) read
+      if (it + 2 < n_tiles) {
+        if (it >= 1) mbar_wait(pv_done + 8 * ((it - 1) % G::VSTAGES), ((it - 1) / G::VSTAGES) & 1);
+        load_v(it + 2, ev);
+      }
+      cp_async_commit();
+      ev = v_entry(it + 3);
+    }
+    cp_async_wait<0>();
+  } else {
+    // ================================ softmax warps: thread = query row ================================
+    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+    const float slope_l2 = p.alibi_slopes ? p.alibi_slopes[head] * kLog2e : 0.f;
+    const bool has_alibi = p.alibi_slopes != nullptr;
+    const int m = m0 + tid;
+    float m_ref = kNegBig, l_run = 0.f;
 
     for (int it = 0; it < n_tiles; ++it) {
       const bool is_ctx = it < n_ctx;
@@ -813,15 +833,6 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
       tc_st32(ts, pw);  // P over its own S columns: the A operand of P.V, read from Tensor Memory
       tc_wait_st();
       l_run = l_run * alpha + sum;
-      // V(it+2) into the stage PV(it-1) has long finished with; then make sure this thread's share of V(it) landed
-      if (it + 2 < n_tiles) {
-        if (it >= 1) mbar_wait(pv_done + 8 * ((it - 1) % G::VSTAGES), ((it - 1) / G::VSTAGES) & 1);
-        load_v(it + 2, ev);
-      }
-      cp_async_commit();
-      ev = v_entry(it + 3);
-      cp_async_wait<2>();
-      fence_proxy_async();
       tc_fence_before();
       mbar_arrive(p_full + 8 * (it & 1));
     }
@@ -866,11 +877,11 @@ static int launch_ws(const PrefillParams& kp, int batch, int max_query_len, cuda
   int dev = 0;
   B200PA_CUDA_CHECK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !configured[dev]) {
-    B200PA_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM + 64));
+    B200PA_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM + 128));
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   dim3 grid(kp.num_heads, (max_query_len + kBM - 1) / kBM, batch);
-  kernel<<<grid, kWsThreads, G::SMEM + 64, stream>>>(kp);
+  kernel<<<grid, kWsThreads, G::SMEM + 128, stream>>>(kp);
   B200PA_CUDA_CHECK(cudaGetLastError());
   return B200PA_OK;
 }
