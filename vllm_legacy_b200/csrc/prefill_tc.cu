@@ -150,6 +150,20 @@ __device__ __forceinline__ float ex2(float x) {
   return y;
 }
 
+// Packed fp32x2 arithmetic (sm_100 FFMA2 / FADD2): two softmax elements per instruction.
+__device__ __forceinline__ void fma2(float& d0, float& d1, float a0, float a1, float b, float c) {
+  asm("{\n.reg .b64 ra, rb, rc, rd;\nmov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %4};\nmov.b64 rc, {%5, %5};\n"
+      "fma.rn.f32x2 rd, ra, rb, rc;\nmov.b64 {%0, %1}, rd;\n}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b), "f"(c));
+}
+__device__ __forceinline__ void add2(float& d0, float& d1, float a0, float a1) {
+  asm("{\n.reg .b64 ra, rd;\nmov.b64 ra, {%2, %3};\nmov.b64 rd, {%0, %1};\nadd.rn.f32x2 rd, rd, ra;\n"
+      "mov.b64 {%0, %1}, rd;\n}"
+      : "+f"(d0), "+f"(d1)
+      : "f"(a0), "f"(a1));
+}
+
 template <int DP>
 struct Geometry {
   static constexpr int QBYTES = kBM * DP * 2;  // [D/8][128 rows][16 B]
@@ -820,16 +834,18 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
         }
         tc_wait_st();
       }
-      float sum = 0.f;
+      float sum = 0.f, sum1 = 0.f;
       const float neg_ref = -m_ref;
       uint32_t pw[BN / 2];
 #pragma unroll
       for (int c = 0; c < BN / 2; ++c) {
-        const float p0 = ex2(fmaf(__uint_as_float(sr[2 * c]), mult, neg_ref));
-        const float p1 = ex2(fmaf(__uint_as_float(sr[2 * c + 1]), mult, neg_ref));
-        sum += p0 + p1;
+        float a0, a1;
+        fma2(a0, a1, __uint_as_float(sr[2 * c]), __uint_as_float(sr[2 * c + 1]), mult, neg_ref);
+        const float p0 = ex2(a0), p1 = ex2(a1);
+        add2(sum, sum1, p0, p1);
         pw[c] = pack2<T>(p0, p1);
       }
+      sum += sum1;
       tc_st32(ts, pw);  // P over its own S columns: the A operand of P.V, read from Tensor Memory
       tc_wait_st();
       l_run = l_run * alpha + sum;
