@@ -24,6 +24,7 @@ EXT = os.path.join(PKG, "_C.so")
 HEAD_SIZES = (64, 80, 96, 112, 128, 192, 256)
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-I", INC, "-I", CSRC]
+NVCC_FLAGS += os.environ.get("B200PA_EXTRA_NVCC_FLAGS", "").split()  # developer builds (e.g. -DB200PA_PREFILL_TRACE)
 
 
 def _headers():

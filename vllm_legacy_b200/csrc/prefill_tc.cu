@@ -30,6 +30,18 @@
 namespace b200pa {
 namespace prefill_tc {
 
+// Developer-only phase timestamps of CTA (0, 0, 0) (tools/prefill_trace.py): compiled out of the product build.
+#ifdef B200PA_PREFILL_TRACE
+__device__ long long g_trace[128 * 16];
+#define B200PA_TRACE(it, slot)                                                                   \
+  do {                                                                                           \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (threadIdx.x & 31) == 0 && (it) < 128) \
+      g_trace[(it) * 16 + (slot)] = clock64();                                                   \
+  } while (0)
+#else
+#define B200PA_TRACE(it, slot) do { } while (0)
+#endif
+
 constexpr int kThreads = 128;
 constexpr int kBM = 128;
 constexpr int kBN = 64;
@@ -60,6 +72,22 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "@P1 bra TC_DONE;\n"
       "bra TC_WAIT;\n"
       "TC_DONE:\n"
+      "}" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+// Same wait for the copy / MMA-issue warps, which spend most of their time waiting: back off between polls so that
+// the spin does not take issue slots from the softmax warps that share their scheduler.
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "TC_RWAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra TC_RDONE;\n"
+      "nanosleep.u32 64;\n"
+      "bra TC_RWAIT;\n"
+      "TC_RDONE:\n"
       "}" ::"r"(bar),
       "r"(parity)
       : "memory");
@@ -521,15 +549,22 @@ __global__ void __launch_bounds__(kThreads, 2) context_attention_tc_kernel(const
 // No __syncthreads in the main loop.  Tensor-pipe order: QK(0), QK(1), PV(0), QK(2), PV(1), ... so the next S is
 // always being computed while the softmax warps work on the current one.
 // ====================================================================================================
-constexpr int kWsThreads = 192;
+constexpr int kWsProducerWarps = 3;  // warp 4 NQ: MMA issue; 4 NQ + 1: V copies; 4 NQ + 2: Q / K copies
 
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 
-template <typename T, int DP>
-__global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(const __grid_constant__ PrefillParams p) {
+// NQ = query heads per CTA.  With NQ = 2 the CTA serves two query heads of one GQA group against the SAME staged
+// K/V tiles (the L2 -> shared-memory copies, not the math, bound the NQ = 1 kernel: removing them took it from
+// 640 to 1025 TFLOP/s), with 8 softmax warps, all 512 TMEM columns and one CTA per SM.
+template <typename T, int DP, int NQ>
+__global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
+    context_attention_ws_kernel(const __grid_constant__ PrefillParams p) {
   using G = Geometry<DP>;
+  constexpr int QBYTES = NQ * G::QBYTES;
+  constexpr int TMEM_COLS = NQ * 256;
+  constexpr int MMA_WARP = 4 * NQ, V_WARP = 4 * NQ + 1, K_WARP = 4 * NQ + 2;
   constexpr int BM = kBM, BN = kBN;
   constexpr int DG = DP / 8;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -538,7 +573,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
   const int warp = tid >> 5;
   const int lane = tid & 31;
 
-  const int head = blockIdx.x;
+  const int head = blockIdx.x * NQ;  // first of the NQ adjacent query heads (same KV head)
   const int mt_idx = gridDim.y - 1 - blockIdx.y;
   const int seq = blockIdx.z;
   const int ctx_len = p.ctx_lens[seq];
@@ -563,44 +598,46 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
   const int n_tiles = n_ctx + (j_end - j_first);
 
   const uint32_t q_smem = smem_u32(smem);
-  const uint32_t k_smem = q_smem + G::QBYTES;
+  const uint32_t k_smem = q_smem + QBYTES;
   const uint32_t v_smem = k_smem + 2 * G::KBYTES;
   const uint32_t bars = v_smem + G::VSTAGES * G::VBYTES;
-  const uint32_t s_full = bars, p_full = bars + 16, pv_done = bars + 32, v_full = bars + 56;  // 2 + 2 + 3 + 3 barriers
-  constexpr int kSlotOff = G::QBYTES + 2 * G::KBYTES + G::VSTAGES * G::VBYTES + 96;
+  // s_full[NQ][2] | p_full[NQ][2] | pv_done[3] | v_full[3] | k_full[2]   (8 bytes each)
+  const uint32_t s_full = bars, p_full = bars + 16 * NQ, pv_done = bars + 32 * NQ, v_full = pv_done + 24;
+  const uint32_t k_full = v_full + 24;
+  constexpr int kSlotOff = QBYTES + 2 * G::KBYTES + G::VSTAGES * G::VBYTES + 32 * NQ + 64 + 8;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kSlotOff);
 
-  if (warp == 4) {
+  if (warp == MMA_WARP) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "n"(G::TMEM_COLS)
+                 "n"(TMEM_COLS)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   } else if (tid == 0) {
-    mbar_init(s_full, 1);
-    mbar_init(s_full + 8, 1);
-    mbar_init(p_full, 128);
-    mbar_init(p_full + 8, 128);
+    for (int i = 0; i < 2 * NQ; ++i) {
+      mbar_init(s_full + 8 * i, 1);
+      mbar_init(p_full + 8 * i, 128);
+    }
     for (int s = 0; s < G::VSTAGES; ++s) mbar_init(pv_done + 8 * s, 1);
     for (int s = 0; s < G::VSTAGES; ++s) mbar_init(v_full + 8 * s, 1);
+    mbar_init(k_full, 1);
+    mbar_init(k_full + 8, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_o = tmem_base + 2 * BN;
 
-  if (warp == 4) {
-    // ================================ producer + MMA issuer ================================
+  if (warp == K_WARP) {
+    // ================================ Q / K loader ================================
+    // (A copy warp blocks in the cp.async issue while the L2 -> shared-memory path is busy -- measured ~1000 clocks
+    // per 16 KB K tile -- so the copies live in warps of their own and the MMA warp below only issues MMAs.)
     const T* kc = static_cast<const T*>(p.k_cache) + (int64_t)kv_head * p.kc_head_stride;
-    const T* vc = static_cast<const T*>(p.v_cache) + (int64_t)kv_head * p.vc_head_stride;
     const T* kn = static_cast<const T*>(p.k) + tok0 * p.k_stride_t + (int64_t)kv_head * p.k_stride_h;
-    const T* vn = static_cast<const T*>(p.v) + tok0 * p.v_stride_t + (int64_t)kv_head * p.v_stride_h;
     const int* table = p.block_tables + (int64_t)seq * p.block_table_stride;
 
-    // lane l copies tokens l and l + 32 of a K / new-V tile and the 8-token group l % 8 of a cached V tile, so it
-    // needs three block-table entries per tile; they are fetched one refill ahead (ek0 / ek1 / ev) so that no
-    // copy ever waits on a dependent global load.
+    // lane l copies tokens l and l + 32 of a K tile, so it needs two block-table entries per tile; they are fetched
+    // one refill ahead (ek0 / ek1) so that no copy ever waits on a dependent global load.
     auto k_entry = [&](int it, int h) -> int {
       const int kpos = (c_first + it) * BN + lane + 32 * h;
       return (it < n_ctx && kpos < ctx_len) ? table[kpos >> bshift] : -1;
@@ -635,14 +672,16 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
     {  // Q: rows lane, lane + 32, lane + 64, lane + 96
       const T* qb = static_cast<const T*>(p.q) + tok0 * p.q_stride_t + (int64_t)head * p.q_stride_h;
 #pragma unroll
-      for (int h = 0; h < 4; ++h) {
-        const int r = lane + 32 * h;
+      for (int h = 0; h < 4 * NQ; ++h) {
+        const int r = lane + 32 * (h & 3);
+        const int jq = h >> 2;  // which of the CTA's heads
         const bool rv = m0 + r < q_len;
-        const T* src = qb + (int64_t)(m0 + r) * p.q_stride_t;
+        const T* src = qb + (int64_t)(m0 + r) * p.q_stride_t + (int64_t)jq * p.q_stride_h;
 #pragma unroll
         for (int c = 0; c < DG; ++c) {
           const bool ok = rv && c * 8 < D;
-          cp_async16(q_smem + c * (BM * 16) + r * 16, ok ? (const void*)(src + c * 8) : (const void*)qb, ok ? 16 : 0);
+          cp_async16(q_smem + jq * G::QBYTES + c * (BM * 16) + r * 16, ok ? (const void*)(src + c * 8) : (const void*)qb,
+                     ok ? 16 : 0);
         }
       }
     }
@@ -652,60 +691,80 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
     cp_async_commit();  // G: K(1)
     int ek0 = k_entry(2, 0), ek1 = k_entry(2, 1);  // for the refill of iteration 0
 
-    constexpr uint32_t idesc_qk = make_idesc<T>(BM, BN, 0);
-    constexpr uint32_t idesc_pv_k = make_idesc<T>(BM, DP, 0);
-    constexpr uint32_t idesc_pv_mn = make_idesc<T>(BM, DP, 1);
-    auto issue_qk = [&](int it) {
-      const uint32_t kb = k_smem + (it & 1) * G::KBYTES;
-#pragma unroll
-      for (int ks = 0; ks < DP / 16; ++ks) {
-        const uint64_t a = make_desc(q_smem + ks * 2 * (BM * 16), BM * 16, 128);
-        const uint64_t b = make_desc(kb + ks * 2 * (BN * 16), BN * 16, 128);
-        tc_mma(tmem_base + (it & 1) * BN, a, b, idesc_qk, ks > 0 ? 1u : 0u);
-      }
-      tc_commit(s_full + 8 * (it & 1));
-    };
-
-    cp_async_wait<1>();  // Q, K(0)
-    fence_proxy_async();
-    __syncwarp();
-    if (lane == 0) issue_qk(0);
 
     for (int it = 0; it < n_tiles; ++it) {
-      cp_async_wait<0>();  // K(it+1) has landed (this lane's part; the fence + syncwarp cover the warp)
-      const bool is_ctx = it < n_ctx;
-      const uint32_t vb = v_smem + (it % G::VSTAGES) * G::VBYTES;
+      cp_async_wait<1>();  // Q and K(it) have landed (this lane's share)
       fence_proxy_async();
       __syncwarp();
-      if (lane == 0 && it + 1 < n_tiles) {
-        tc_fence_after();
-        issue_qk(it + 1);
-      }
-      // refill K(it+2) once QK(it) has finished with its stage (the softmax warps stage V, see below)
+      if (lane == 0) mbar_arrive(k_full + 8 * (it & 1));
+      // K(it+2) goes into the stage QK(it) reads: wait for the last head's QK(it)
       if (it + 2 < n_tiles) {
-        mbar_wait(s_full + 8 * (it & 1), (it >> 1) & 1);
+        mbar_wait_relaxed(s_full + 16 * (NQ - 1) + 8 * (it & 1), (it >> 1) & 1);
         load_k(it + 2, ek0, ek1);
       }
       cp_async_commit();
       ek0 = k_entry(it + 3, 0);
       ek1 = k_entry(it + 3, 1);
-      // V(it) has landed (warp 5) and P(it) is in TMEM (softmax warps): O += P(it) V(it)
-      mbar_wait(v_full + 8 * (it % G::VSTAGES), (it / G::VSTAGES) & 1);
-      mbar_wait(p_full + 8 * (it & 1), (it >> 1) & 1);
-      tc_fence_after();
-      if (lane == 0) {
-#pragma unroll
-        for (int kk = 0; kk < BN / 16; ++kk) {
-          const uint64_t b = make_desc(vb + kk * 2 * (DP * 16), DP * 16, 128);
-          tc_mma_ts(tmem_o, tmem_base + (it & 1) * BN + kk * 8, b, is_ctx ? idesc_pv_k : idesc_pv_mn,
-                    (it > 0 || kk > 0) ? 1u : 0u);
-        }
-        tc_commit(pv_done + 8 * (it % G::VSTAGES));
-      }
-      __syncwarp();
     }
     cp_async_wait<0>();
-  } else if (warp == 5) {
+  } else if (warp == MMA_WARP) {
+    // ================================ MMA issuer ================================
+    constexpr uint32_t idesc_qk = make_idesc<T>(BM, BN, 0);
+    constexpr uint32_t idesc_pv_k = make_idesc<T>(BM, DP, 0);
+    constexpr uint32_t idesc_pv_mn = make_idesc<T>(BM, DP, 1);
+    auto issue_qk = [&](int it) {  // S_j(it & 1) = Q_j K(it)^T for every head j of the CTA
+      const uint32_t kb = k_smem + (it & 1) * G::KBYTES;
+#pragma unroll
+      for (int jq = 0; jq < NQ; ++jq) {
+#pragma unroll
+        for (int ks = 0; ks < DP / 16; ++ks) {
+          const uint64_t a = make_desc(q_smem + jq * G::QBYTES + ks * 2 * (BM * 16), BM * 16, 128);
+          const uint64_t b = make_desc(kb + ks * 2 * (BN * 16), BN * 16, 128);
+          tc_mma(tmem_base + jq * 256 + (it & 1) * BN, a, b, idesc_qk, ks > 0 ? 1u : 0u);
+        }
+        tc_commit(s_full + 16 * jq + 8 * (it & 1));
+      }
+    };
+
+
+    mbar_wait_relaxed(k_full, 0);  // Q, K(0)
+    tc_fence_after();
+    if (lane == 0) issue_qk(0);
+    __syncwarp();
+
+    for (int it = 0; it < n_tiles; ++it) {
+      B200PA_TRACE(it, 4);
+      const bool is_ctx = it < n_ctx;
+      const uint32_t vb = v_smem + (it % G::VSTAGES) * G::VBYTES;
+      if (it + 1 < n_tiles) {
+        mbar_wait_relaxed(k_full + 8 * ((it + 1) & 1), ((it + 1) >> 1) & 1);
+        B200PA_TRACE(it, 5);
+        tc_fence_after();
+        if (lane == 0) issue_qk(it + 1);
+        __syncwarp();
+      }
+      B200PA_TRACE(it, 6);
+      // V(it) has landed (V loader) and P(it) is in TMEM (softmax warps): O += P(it) V(it)
+      mbar_wait_relaxed(v_full + 8 * (it % G::VSTAGES), (it / G::VSTAGES) & 1);
+      B200PA_TRACE(it, 8);
+#pragma unroll
+      for (int jq = 0; jq < NQ; ++jq) {
+        mbar_wait_relaxed(p_full + 16 * jq + 8 * (it & 1), (it >> 1) & 1);
+        tc_fence_after();
+        if (lane == 0) {
+#pragma unroll
+          for (int kk = 0; kk < BN / 16; ++kk) {
+            const uint64_t b = make_desc(vb + kk * 2 * (DP * 16), DP * 16, 128);
+            tc_mma_ts(tmem_base + jq * 256 + 2 * BN, tmem_base + jq * 256 + (it & 1) * BN + kk * 8, b,
+                      is_ctx ? idesc_pv_k : idesc_pv_mn, (it > 0 || kk > 0) ? 1u : 0u);
+          }
+          if (jq == NQ - 1) tc_commit(pv_done + 8 * (it % G::VSTAGES));  // covers every head's PV(it)
+        }
+        __syncwarp();
+        B200PA_TRACE(it, 9 + jq);
+      }
+    }
+  } else if (warp == V_WARP) {
     // ================================ V loader ================================
     // Lane l always copies the 8-token group l % 8 (cached V: rows l / 8, l / 8 + 4, ...) or tokens l and l + 32
     // (new V), so it needs one block-table entry per tile, fetched a tile ahead.  Tokens >= ctx_len inside the last
@@ -759,7 +818,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
       if (lane == 0) mbar_arrive(v_full + 8 * (it % G::VSTAGES));
       // V(it+2) goes into the stage PV(it-1) read
       if (it + 2 < n_tiles) {
-        if (it >= 1) mbar_wait(pv_done + 8 * ((it - 1) % G::VSTAGES), ((it - 1) / G::VSTAGES) & 1);
+        if (it >= 1) mbar_wait_relaxed(pv_done + 8 * ((it - 1) % G::VSTAGES), ((it - 1) / G::VSTAGES) & 1);
         load_v(it + 2, ev);
       }
       cp_async_commit();
@@ -768,18 +827,26 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
     cp_async_wait<0>();
   } else {
     // ================================ softmax warps: thread = query row ================================
-    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
-    const float slope_l2 = p.alibi_slopes ? p.alibi_slopes[head] * kLog2e : 0.f;
+    const int jq = warp >> 2;                 // this warp's head inside the CTA
+    const int row = tid & 127;                // query row = TMEM lane
+    const int my_head = head + jq;
+    const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t tmem_q = tmem_base + jq * 256;   // S0 | S1 | O of this head
+    const uint32_t tmem_o = tmem_q + 2 * BN;
+    const uint32_t s_full_q = s_full + 16 * jq, p_full_q = p_full + 16 * jq;
+    const float slope_l2 = p.alibi_slopes ? p.alibi_slopes[my_head] * kLog2e : 0.f;
     const bool has_alibi = p.alibi_slopes != nullptr;
-    const int m = m0 + tid;
+    const int m = m0 + row;
     float m_ref = kNegBig, l_run = 0.f;
 
     for (int it = 0; it < n_tiles; ++it) {
       const bool is_ctx = it < n_ctx;
       const int t0 = is_ctx ? (c_first + it) * BN : (j_first + it - n_ctx) * BN;
-      mbar_wait(s_full + 8 * (it & 1), (it >> 1) & 1);
+      if (warp == 0) B200PA_TRACE(it, 0);
+      mbar_wait(s_full_q + 8 * (it & 1), (it >> 1) & 1);
+      if (warp == 0) B200PA_TRACE(it, 1);
       tc_fence_after();
-      const uint32_t ts = tmem_base + (it & 1) * BN + lane_off;
+      const uint32_t ts = tmem_q + (it & 1) * BN + lane_off;
       uint32_t sr[BN];
       {
         uint32_t (&lo)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sr[0]);
@@ -834,6 +901,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
         }
         tc_wait_st();
       }
+      if (warp == 0) B200PA_TRACE(it, 2);
       float sum = 0.f, sum1 = 0.f;
       const float neg_ref = -m_ref;
       uint32_t pw[BN / 2];
@@ -850,13 +918,14 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
       tc_wait_st();
       l_run = l_run * alpha + sum;
       tc_fence_before();
-      mbar_arrive(p_full + 8 * (it & 1));
+      mbar_arrive(p_full_q + 8 * (it & 1));
+      if (warp == 0) B200PA_TRACE(it, 3);
     }
     mbar_wait(pv_done + 8 * ((n_tiles - 1) % G::VSTAGES), ((n_tiles - 1) / G::VSTAGES) & 1);
     tc_fence_after();
     {
       const float inv = 1.f / l_run;
-      T* orow = static_cast<T*>(p.out) + (tok0 + m) * p.o_stride_t + (int64_t)head * p.o_stride_h;
+      T* orow = static_cast<T*>(p.out) + (tok0 + m) * p.o_stride_t + (int64_t)my_head * p.o_stride_h;
 #pragma unroll 1
       for (int c0 = 0; c0 < DP; c0 += 32) {
         uint32_t o[32];
@@ -880,26 +949,37 @@ __global__ void __launch_bounds__(kWsThreads, 2) context_attention_ws_kernel(con
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(G::TMEM_COLS) : "memory");
+  if (warp == MMA_WARP) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
   }
 }
 
-template <typename T, int DP>
-static int launch_ws(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
+template <typename T, int DP, int NQ>
+static int launch_ws_nq(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
   using G = Geometry<DP>;
-  auto kernel = context_attention_ws_kernel<T, DP>;
+  auto kernel = context_attention_ws_kernel<T, DP, NQ>;
+  constexpr int kSmem = NQ * G::QBYTES + 2 * G::KBYTES + G::VSTAGES * G::VBYTES + 256;
   static bool configured[64] = {false};
   int dev = 0;
   B200PA_CUDA_CHECK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !configured[dev]) {
-    B200PA_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM + 128));
+    B200PA_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
-  dim3 grid(kp.num_heads, (max_query_len + kBM - 1) / kBM, batch);
-  kernel<<<grid, kWsThreads, G::SMEM + 128, stream>>>(kp);
+  dim3 grid(kp.num_heads / NQ, (max_query_len + kBM - 1) / kBM, batch);
+  kernel<<<grid, NQ * 128 + 32 * kWsProducerWarps, kSmem, stream>>>(kp);
   B200PA_CUDA_CHECK(cudaGetLastError());
   return B200PA_OK;
+}
+
+// Two query heads per CTA whenever the GQA group has an even number of heads (they share every K/V tile).
+template <typename T, int DP>
+static int launch_ws(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
+  static const int nq_knob = [] { const char* e = std::getenv("B200PA_PREFILL_NQ"); return e ? std::atoi(e) : 0; }();
+  const int group = kp.num_heads / kp.num_kv_heads;
+  const bool two = nq_knob ? nq_knob == 2 : true;
+  if (two && group % 2 == 0) return launch_ws_nq<T, DP, 2>(kp, batch, max_query_len, stream);
+  return launch_ws_nq<T, DP, 1>(kp, batch, max_query_len, stream);
 }
 
 template <typename T, int DP>
@@ -951,3 +1031,9 @@ int launch_prefill_tc(const PrefillParams& kp, int batch, int max_query_len, int
 }
 
 }  // namespace b200pa
+
+#ifdef B200PA_PREFILL_TRACE
+extern "C" int b200pa_debug_prefill_trace(long long* out, int n) {
+  return (int)cudaMemcpyFromSymbol(out, b200pa::prefill_tc::g_trace, sizeof(long long) * (size_t)n);
+}
+#endif
