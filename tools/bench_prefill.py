@@ -20,6 +20,7 @@ CASES = {
     "llama8b_chunk512_ctx8k": (32, 4, 128, 16, [(512, 8192)] * 16, torch.bfloat16),
     "llama8b_prefix1k_new1k": (32, 4, 128, 16, [(1024, 1024)] * 16, torch.bfloat16),
     "llama70b_tp8_chunk2k_ctx4k": (8, 8, 128, 16, [(2048, 4096)] * 8, torch.bfloat16),
+    "llama7b_mha_chunk2k_ctx4k": (32, 1, 128, 16, [(2048, 4096)] * 8, torch.bfloat16),
     "ref_test_shape_fp16": (64, 8, 128, 32, None, torch.float16),
     "window256_chunk2k_ctx4k": (32, 4, 128, 16, [(2048, 4096)] * 8, torch.bfloat16),
 }

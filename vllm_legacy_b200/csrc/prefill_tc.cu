@@ -558,7 +558,10 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 // NQ = query heads per CTA.  With NQ = 2 the CTA serves two query heads of one GQA group against the SAME staged
 // K/V tiles (the L2 -> shared-memory copies, not the math, bound the NQ = 1 kernel: removing them took it from
 // 640 to 1025 TFLOP/s), with 8 softmax warps, all 512 TMEM columns and one CTA per SM.
-template <typename T, int DP, int NQ>
+// ROWS = false: the NQ tiles are the same 128 rows of NQ adjacent heads (GQA groups with an even head count);
+// ROWS = true: they are NQ consecutive 128-row tiles of ONE head (MHA / odd groups): the CTA walks the K/V range of
+// its last tile and the earlier tile sees the up to two extra causal tiles fully masked (p = 0).
+template <typename T, int DP, int NQ, bool ROWS>
 __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
     context_attention_ws_kernel(const __grid_constant__ PrefillParams p) {
   using G = Geometry<DP>;
@@ -573,12 +576,13 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
   const int warp = tid >> 5;
   const int lane = tid & 31;
 
-  const int head = blockIdx.x * NQ;  // first of the NQ adjacent query heads (same KV head)
+  const int head = blockIdx.x * (ROWS ? 1 : NQ);  // first of the NQ adjacent query heads (same KV head)
+  constexpr int CTA_ROWS = ROWS ? NQ * kBM : kBM;
   const int mt_idx = gridDim.y - 1 - blockIdx.y;
   const int seq = blockIdx.z;
   const int ctx_len = p.ctx_lens[seq];
   const int q_len = p.seq_lens[seq] - ctx_len;
-  const int m0 = mt_idx * BM;
+  const int m0 = mt_idx * CTA_ROWS;  // first query row of the CTA
   if (m0 >= q_len) return;
   const int64_t tok0 = p.start_loc[seq];
   const int kv_head = head / (p.num_heads / p.num_kv_heads);
@@ -593,7 +597,7 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
     j_first = max(0, m0 - W + 1) / BN;
   }
   const int c_end = (ctx_len + BN - 1) / BN;
-  const int j_end = (min(q_len, m0 + BM) + BN - 1) / BN;
+  const int j_end = (min(q_len, m0 + CTA_ROWS) + BN - 1) / BN;
   const int n_ctx = max(0, c_end - c_first);
   const int n_tiles = n_ctx + (j_end - j_first);
 
@@ -675,8 +679,9 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
       for (int h = 0; h < 4 * NQ; ++h) {
         const int r = lane + 32 * (h & 3);
         const int jq = h >> 2;  // which of the CTA's heads
-        const bool rv = m0 + r < q_len;
-        const T* src = qb + (int64_t)(m0 + r) * p.q_stride_t + (int64_t)jq * p.q_stride_h;
+        const int qm = m0 + r + (ROWS ? jq * BM : 0);
+        const bool rv = qm < q_len;
+        const T* src = qb + (int64_t)qm * p.q_stride_t + (int64_t)(ROWS ? 0 : jq) * p.q_stride_h;
 #pragma unroll
         for (int c = 0; c < DG; ++c) {
           const bool ok = rv && c * 8 < D;
@@ -829,14 +834,15 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
     // ================================ softmax warps: thread = query row ================================
     const int jq = warp >> 2;                 // this warp's head inside the CTA
     const int row = tid & 127;                // query row = TMEM lane
-    const int my_head = head + jq;
+    const int my_head = head + (ROWS ? 0 : jq);
+    const int m0_q = m0 + (ROWS ? jq * BM : 0);  // first row of this warp's tile
     const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t tmem_q = tmem_base + jq * 256;   // S0 | S1 | O of this head
     const uint32_t tmem_o = tmem_q + 2 * BN;
     const uint32_t s_full_q = s_full + 16 * jq, p_full_q = p_full + 16 * jq;
     const float slope_l2 = p.alibi_slopes ? p.alibi_slopes[my_head] * kLog2e : 0.f;
     const bool has_alibi = p.alibi_slopes != nullptr;
-    const int m = m0 + row;
+    const int m = m0_q + row;
     float m_ref = kNegBig, l_run = 0.f;
 
     for (int it = 0; it < n_tiles; ++it) {
@@ -859,9 +865,9 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
       const int col_limit = is_ctx ? (ctx_len - t0) : BN;
       bool need_mask;
       if (is_ctx)
-        need_mask = (t0 + BN > ctx_len) || (W > 0 && ctx_len + m0 + BM - 1 - t0 >= W);
+        need_mask = (t0 + BN > ctx_len) || (W > 0 && ctx_len + m0_q + BM - 1 - t0 >= W);
       else
-        need_mask = (t0 + BN - 1 > m0) || (W > 0 && m0 + BM - 1 - t0 >= W);
+        need_mask = (t0 + BN - 1 > m0_q) || (W > 0 && m0_q + BM - 1 - t0 >= W);
       float mx = kNegBig;
       float mult;  // p = 2^(sr * mult - m_ref)
       if (need_mask || has_alibi) {
@@ -954,10 +960,11 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
   }
 }
 
-template <typename T, int DP, int NQ>
+template <typename T, int DP, int NQ, bool ROWS>
 static int launch_ws_nq(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
   using G = Geometry<DP>;
-  auto kernel = context_attention_ws_kernel<T, DP, NQ>;
+  auto kernel = context_attention_ws_kernel<T, DP, NQ, ROWS>;
+  constexpr int kCtaRows = ROWS ? NQ * kBM : kBM;
   constexpr int kSmem = NQ * G::QBYTES + 2 * G::KBYTES + G::VSTAGES * G::VBYTES + 256;
   static bool configured[64] = {false};
   int dev = 0;
@@ -966,20 +973,23 @@ static int launch_ws_nq(const PrefillParams& kp, int batch, int max_query_len, c
     B200PA_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
-  dim3 grid(kp.num_heads / NQ, (max_query_len + kBM - 1) / kBM, batch);
+  dim3 grid(kp.num_heads / (ROWS ? 1 : NQ), (max_query_len + kCtaRows - 1) / kCtaRows, batch);
   kernel<<<grid, NQ * 128 + 32 * kWsProducerWarps, kSmem, stream>>>(kp);
   B200PA_CUDA_CHECK(cudaGetLastError());
   return B200PA_OK;
 }
 
-// Two query heads per CTA whenever the GQA group has an even number of heads (they share every K/V tile).
+// Two Q tiles per CTA share every staged K/V tile: two heads of a GQA group with an even head count, else two
+// consecutive row tiles of one head when the prompts are longer than one tile.  B200PA_PREFILL_NQ (developer knob):
+// 1 = one tile per CTA, 3 = row pairs even where head pairs apply.
 template <typename T, int DP>
 static int launch_ws(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
   static const int nq_knob = [] { const char* e = std::getenv("B200PA_PREFILL_NQ"); return e ? std::atoi(e) : 0; }();
   const int group = kp.num_heads / kp.num_kv_heads;
-  const bool two = nq_knob ? nq_knob == 2 : true;
-  if (two && group % 2 == 0) return launch_ws_nq<T, DP, 2>(kp, batch, max_query_len, stream);
-  return launch_ws_nq<T, DP, 1>(kp, batch, max_query_len, stream);
+  if (nq_knob == 1) return launch_ws_nq<T, DP, 1, false>(kp, batch, max_query_len, stream);
+  if (group % 2 == 0 && nq_knob != 3) return launch_ws_nq<T, DP, 2, false>(kp, batch, max_query_len, stream);
+  if (max_query_len > kBM || nq_knob == 3) return launch_ws_nq<T, DP, 2, true>(kp, batch, max_query_len, stream);
+  return launch_ws_nq<T, DP, 1, false>(kp, batch, max_query_len, stream);
 }
 
 template <typename T, int DP>
