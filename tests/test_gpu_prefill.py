@@ -196,6 +196,33 @@ def test_random_ragged_batches(ops, seed):
     torch.testing.assert_close(out.float(), ref, atol=atol, rtol=1e-2)
 
 
+@pytest.mark.parametrize("qpk", [1, 2, 3])
+@pytest.mark.parametrize("mode", ["plain", "window", "alibi"])
+@pytest.mark.parametrize("head_size", [64, 128])
+@torch.inference_mode()
+def test_q_tile_pairing(ops, qpk, mode, head_size):
+    """The tcgen05 kernel pairs two Q tiles per CTA: two heads of an even GQA group (qpk 2), else two consecutive
+    128-row tiles of one head (qpk 1 and 3).  Query lengths sit on every side of the 128 / 256-row edges so that the
+    second tile of a pair is empty, partial or full, with and without a prefix; the 130-token window makes the first
+    tiles of the upper tile fully masked before it has seen a visible key."""
+    query_lens = [1, 127, 128, 129, 255, 256, 257, 385, 600]
+    ctx_lens = [300, 0, 64, 5, 0, 1000, 33, 129, 0]
+    num_heads = 2 * qpk
+    case = helpers.make_prefill_case(num_heads, qpk, head_size, torch.bfloat16, DEV, query_lens=query_lens,
+                                     ctx_lens=ctx_lens, block_size=16, amplitude=1.0, seed=7 + qpk, stale_nan=True)
+    slopes = _alibi_slopes(num_heads).to(DEV) if mode == "alibi" else None
+    window = 130 if mode == "window" else 0
+    out = _run(ops, case, slopes, window)
+    ref = helpers.ref_context_attention(case, slopes, window)
+    assert not torch.isnan(out).any()
+    torch.testing.assert_close(out.float(), ref, atol=4e-3, rtol=1e-2)
+    # one-tile prompts with an odd group take the single-tile kernel
+    short = helpers.make_prefill_case(num_heads, qpk, head_size, torch.bfloat16, DEV, query_lens=[128, 70, 3],
+                                      ctx_lens=[200, 0, 17], block_size=16, amplitude=1.0, seed=11, stale_nan=True)
+    out = _run(ops, short, slopes, window)
+    torch.testing.assert_close(out.float(), helpers.ref_context_attention(short, slopes, window), atol=4e-3, rtol=1e-2)
+
+
 @torch.inference_mode()
 def test_deterministic_and_graph_capturable(ops):
     """Same inputs -> bit-identical output on every launch; the op allocates nothing and never synchronises when the
