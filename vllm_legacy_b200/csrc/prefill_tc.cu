@@ -96,6 +96,20 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity)
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+// One leader lane of a converged warp.  A branch on elect.sync tells the compiler exactly one thread is active, so
+// the uniform-datapath tcgen05 instructions under it are emitted straight; under `if (lane == 0)` every one of them
+// is wrapped in an ELECT / BRA.U.ANY loop (~13 SASS instructions, ~60 clocks per MMA, measured).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "elect.sync _|p, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
+}
 // D[tmem] (+)= A[smem desc] . B[smem desc]
 __device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
   asm volatile(
@@ -734,7 +748,7 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
 
     mbar_wait_relaxed(k_full, 0);  // Q, K(0)
     tc_fence_after();
-    if (lane == 0) issue_qk(0);
+    if (elect_one()) issue_qk(0);
     __syncwarp();
 
     for (int it = 0; it < n_tiles; ++it) {
@@ -745,7 +759,7 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
         mbar_wait_relaxed(k_full + 8 * ((it + 1) & 1), ((it + 1) >> 1) & 1);
         B200PA_TRACE(it, 5);
         tc_fence_after();
-        if (lane == 0) issue_qk(it + 1);
+        if (elect_one()) issue_qk(it + 1);
         __syncwarp();
       }
       B200PA_TRACE(it, 6);
@@ -756,7 +770,7 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
       for (int jq = 0; jq < NQ; ++jq) {
         mbar_wait_relaxed(p_full + 16 * jq + 8 * (it & 1), (it >> 1) & 1);
         tc_fence_after();
-        if (lane == 0) {
+        if (elect_one()) {
 #pragma unroll
           for (int kk = 0; kk < BN / 16; ++kk) {
             const uint64_t b = make_desc(vb + kk * 2 * (DP * 16), DP * 16, 128);
