@@ -74,11 +74,19 @@ def build(force=False, verbose=False):
     with cf.ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 2)) as ex:
         changed = list(ex.map(lambda j: _compile(j[0], j[1], j[2], force, verbose), jobs))
     objs = [j[1] for j in jobs]
-    if any(changed) or not os.path.exists(LIB):
+    # The in-tree library remembers which objects it was linked from (a build from another B200PA_BUILD_DIR, e.g. a
+    # developer build with extra flags, must not survive a later default build whose objects are all up to date).
+    link_stamp = _stamp(["link", *NVCC_FLAGS], [o + ".stamp" for o in objs])
+    link_stamp_file = LIB + ".stamp"
+    linked = os.path.exists(LIB) and os.path.exists(link_stamp_file) and open(link_stamp_file).read() == link_stamp
+    relink = any(changed) or not linked
+    if relink:
         cmd = ["nvcc", "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
         if verbose:
             print("+", " ".join(cmd), flush=True)
         subprocess.check_call(cmd)
+        with open(link_stamp_file, "w") as f:
+            f.write(link_stamp)
 
     # ---- torch extension ------------------------------------------------------------------------
     import torch
@@ -94,7 +102,7 @@ def build(force=False, verbose=False):
     cmd = ["g++", "-c", src, "-o", obj, "-O2", "-fPIC", "-std=c++17", "-w", "-DTORCH_EXTENSION_NAME=_C",
            f"-D_GLIBCXX_USE_CXX11_ABI={abi}", "-DTORCH_API_INCLUDE_EXTENSION_H", "-I", INC, *inc]
     ch = _compile(cmd, obj, [src, os.path.join(INC, "b200pa.h")], force, verbose)
-    if ch or any(changed) or not os.path.exists(EXT):
+    if ch or relink or not os.path.exists(EXT):
         cmd = ["g++", "-shared", "-o", EXT, obj, f"-L{PKG}", "-lb200pa", "-Wl,-rpath,$ORIGIN",
                f"-L{tlib}", f"-Wl,-rpath,{tlib}", "-ltorch", "-ltorch_cpu", "-ltorch_cuda", "-lc10", "-lc10_cuda",
                "-ltorch_python"]
