@@ -380,7 +380,30 @@ def run_reference(args, rank, world):
     }
 
 
+_JSON_FD = None
+
+
+def _stdout_json_only():
+    """stdout carries the one JSON line and nothing else: file descriptor 1 is pointed at stderr for the rest of the
+    run (NCCL prints its version banner on stdout when NCCL_DEBUG is set on the box) and the line is written to the
+    saved descriptor."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def _emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    _stdout_json_only()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
@@ -396,7 +419,7 @@ def main():
     if args.impl == "reference":
         line = run_reference(args, rank, world)
         if line is not None:
-            print(json.dumps(line), flush=True)
+            _emit(line)
         return 0
 
     if not torch.cuda.is_available():
@@ -424,7 +447,7 @@ def main():
                 except Exception as e:  # noqa: BLE001
                     line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "port",
                                             "sample": f"failed: {e}"}
-            print(json.dumps(line), flush=True)
+            _emit(line)
     finally:
         if world > 1:
             dist.barrier()
