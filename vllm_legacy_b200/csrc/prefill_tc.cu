@@ -576,12 +576,13 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 // ROWS = true: they are NQ consecutive 128-row tiles of ONE head (MHA / odd groups): the CTA walks the K/V range of
 // its last tile and the earlier tile sees the up to two extra causal tiles fully masked (p = 0).
 template <typename T, int DP, int NQ, bool ROWS>
-__global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
+__global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
     context_attention_ws_kernel(const __grid_constant__ PrefillParams p) {
   using G = Geometry<DP>;
   constexpr int QBYTES = NQ * G::QBYTES;
   constexpr int TMEM_COLS = NQ * 256;
-  constexpr int MMA_WARP = 4 * NQ, V_WARP = 4 * NQ + 1, K_WARP = 4 * NQ + 2;
+  constexpr int LW = NQ;  // loader warps per operand
+  constexpr int MMA_WARP = 4 * NQ, V_WARP = 4 * NQ + 1, K_WARP = V_WARP + LW;
   constexpr int BM = kBM, BN = kBN;
   constexpr int DG = DP / 8;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -636,9 +637,9 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
       mbar_init(p_full + 8 * i, 128);
     }
     for (int s = 0; s < G::VSTAGES; ++s) mbar_init(pv_done + 8 * s, 1);
-    for (int s = 0; s < G::VSTAGES; ++s) mbar_init(v_full + 8 * s, 1);
-    mbar_init(k_full, 1);
-    mbar_init(k_full + 8, 1);
+    for (int s = 0; s < G::VSTAGES; ++s) mbar_init(v_full + 8 * s, LW);
+    mbar_init(k_full, LW);
+    mbar_init(k_full + 8, LW);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   tc_fence_before();
@@ -646,7 +647,8 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == K_WARP) {
+  if (warp >= K_WARP) {
+    const int lw = warp - K_WARP;  // this loader's share: token halves / Q row groups lw, lw + LW, ...
     // ================================ Q / K loader ================================
     // (A copy warp blocks in the cp.async issue while the L2 -> shared-memory path is busy -- measured ~1000 clocks
     // per 16 KB K tile -- so the copies live in warps of their own and the MMA warp below only issues MMAs.)
@@ -664,7 +666,7 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
       if (it >= n_tiles) return;
       const uint32_t kb = k_smem + (it & 1) * G::KBYTES;
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
+      for (int h = lw; h < 2; h += LW) {
         const int kt = lane + 32 * h;
         const uint32_t dst = kb + kt * 16;  // (token t, d-group g) -> g * (BN * 16) + t * 16
         if (it < n_ctx) {
@@ -690,7 +692,7 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
     {  // Q: rows lane, lane + 32, lane + 64, lane + 96
       const T* qb = static_cast<const T*>(p.q) + tok0 * p.q_stride_t + (int64_t)head * p.q_stride_h;
 #pragma unroll
-      for (int h = 0; h < 4 * NQ; ++h) {
+      for (int h = lw; h < 4 * NQ; h += LW) {
         const int r = lane + 32 * (h & 3);
         const int jq = h >> 2;  // which of the CTA's heads
         const int qm = m0 + r + (ROWS ? jq * BM : 0);
@@ -783,7 +785,8 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
         B200PA_TRACE(it, 9 + jq);
       }
     }
-  } else if (warp == V_WARP) {
+  } else if (warp >= V_WARP) {
+    const int lw = warp - V_WARP;
     // ================================ V loader ================================
     // Lane l always copies the 8-token group l % 8 (cached V: rows l / 8, l / 8 + 4, ...) or tokens l and l + 32
     // (new V), so it needs one block-table entry per tile, fetched a tile ahead.  Tokens >= ctx_len inside the last
@@ -806,13 +809,13 @@ __global__ void __launch_bounds__(NQ * 128 + 96, NQ == 1 ? 2 : 1)
         const T* src = vc + (int64_t)max(phys, 0) * p.vc_block_stride + (kpos & (B - 1));
         const uint32_t dst = vb + (vg >> 3) * (DP * 16);  // (row d, 8 tokens at vg) -> (vg / 8) * (DP * 16) + d * 16
 #pragma unroll 8
-        for (int d = lane >> 3; d < DP; d += 4) {
+        for (int d = (lane >> 3) + 4 * lw; d < DP; d += 4 * LW) {
           const bool ok = phys >= 0 && d < D;
           cp_async16(dst + d * 16, ok ? (const void*)(src + (int64_t)d * B) : (const void*)vc, ok ? nbytes : 0);
         }
       } else {
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
+        for (int h = lw; h < 2; h += LW) {
           const int kt = lane + 32 * h;
           const int j = (j_first + it - n_ctx) * BN + kt;
           const T* src = vn + (int64_t)j * p.v_stride_t;
@@ -988,7 +991,7 @@ static int launch_ws_nq(const PrefillParams& kp, int batch, int max_query_len, c
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   dim3 grid(kp.num_heads / (ROWS ? 1 : NQ), (max_query_len + kCtaRows - 1) / kCtaRows, batch);
-  kernel<<<grid, NQ * 128 + 32 * kWsProducerWarps, kSmem, stream>>>(kp);
+  kernel<<<grid, NQ * 128 + 32 + 64 * NQ, kSmem, stream>>>(kp);
   B200PA_CUDA_CHECK(cudaGetLastError());
   return B200PA_OK;
 }
