@@ -309,12 +309,39 @@ int b200pa_convert_fp8(void* dst, const void* src, int64_t numel, int32_t dst_dt
 /* replaces: csrc/cuda_utils.h, csrc/cuda_utils_kernels.cu:17-29 */
 int b200pa_get_max_shared_memory_per_block_device_attribute(int32_t device_id);
 
+/* replaces: csrc/cuda_utils.h, csrc/cuda_utils_kernels.cu:5-15 (device_id < 0 = current device) */
+int b200pa_get_device_attribute(int32_t attribute, int32_t device_id);
+
+/*
+ * Attention workspace.  The persistent decode kernel cuts the flattened KV-block list of a launch
+ * into equal ranges, one per resident CTA; an item cut by a range boundary leaves partial results
+ * in a per-device workspace (2 slots per CTA + one arrival counter per CTA, ~10 MB), allocated by
+ * the first attention call on a device and kept for the life of the process.  b200pa_prepare()
+ * allocates it explicitly (hosts that capture their very first call into a CUDA graph may prefer
+ * that, although the lazy path is capture-safe too).  Attention calls on ONE device must not run
+ * concurrently on different streams (the reference's worker issues them on one stream).
+ */
+int b200pa_prepare(int32_t device);
+
+/* Developer hook (tools/tune.py, tests): override a tuning knob at run time.  The same knobs are
+ * read from the environment (B200PA_<KEY>) once, when the library is first used — never per call.
+ * Keys: stages, evict_normal, force_simt, partition_size, max_partition, grid_ctas,
+ * min_blocks_per_cta, grid_kernel. */
+int b200pa_set_tuning(const char* key, int32_t value);
+
+/* Index arithmetic of the persistent kernel's work split (csrc/attention_sched.cuh), exported so
+ * that the CPU test-suite exercises the very functions the kernel compiles. */
+int64_t b200pa_sched_range_begin(int64_t total_blocks, int32_t num_ctas, int32_t cta);
+int32_t b200pa_sched_cta_of(int64_t total_blocks, int32_t num_ctas, int64_t flat_index);
+int32_t b200pa_sched_effective_ctas(int64_t total_blocks, int32_t grid);
+
 /* Diagnostics */
 int b200pa_abi_version(void);
 const char* b200pa_status_string(int status);
 int b200pa_last_cuda_error(void); /* cudaError_t of the last B200PA_ERR_CUDA on this thread */
 /* Name of the kernel family the last attention call on this thread dispatched
- * to ("mma_tma" | "simt"), and the split it used; for tests and the bench. */
+ * to ("mma_tma" | "simt"), and the split it used (persistent kernel: CTAs launched;
+ * SIMT family: context partitions); for tests and the bench. */
 const char* b200pa_last_attention_path(void);
 int b200pa_last_attention_partitions(void);
 

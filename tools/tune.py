@@ -1,8 +1,8 @@
 #!/usr/bin/env python3
 """Developer tool (GPU box): time the attention ops on the BASELINE configs under different launch knobs
-(environment variables read by libb200pa at call time).  Prints one line per (config, knob set).
+(b200pa_set_tuning keys; the library reads its environment only once, at load).  One line per (config, knob set).
 
-  python tools/tune.py --configs c2,c4 --knobs "" "B200PA_STAGES=2" "B200PA_STAGES=4,B200PA_MAX_PARTITION=2048"
+  python tools/tune.py --configs c2,c4 --knobs "" "stages=2" "stages=4,evict_normal=1" "grid_kernel=1"
 """
 import argparse
 import math
@@ -36,7 +36,12 @@ CONFIGS = {
     "c5b32": (ragged_lens(), 32, 8, 128, 32, "auto"),
     "small": ([2048] * 8, 32, 8, 128, 16, "auto"),
     "one": ([32768] * 1, 32, 8, 128, 16, "auto"),
+    "mid": ([8192] * 32, 32, 8, 128, 16, "auto"),          # 17-64 sequences: the reference's rule still picks v1
+    "c3tp4": ([8192] * 256, 16, 2, 128, 16, "auto"),
+    "short": ([200] * 1024, 32, 8, 128, 16, "auto"),       # many short sequences: item switches dominate
 }
+DEFAULTS = {"stages": 0, "evict_normal": -1, "force_simt": 0, "partition_size": 0, "max_partition": 4096,
+            "grid_ctas": 0, "min_blocks_per_cta": 8, "grid_kernel": 0}
 
 
 def build(name):
@@ -90,7 +95,15 @@ def timed(fn, iters, warmup=3):
         torch.cuda.synchronize()
         ts.append(e0.elapsed_time(e1))
     ts.sort()
-    return ts[len(ts) // 2], ts[0]
+    # back to back (what bench.py times): 20 launches between two events, no flush (inputs > L2 except c1/small/one)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return ts[len(ts) // 2], ts[0], e0.elapsed_time(e1) / 20
 
 
 def main():
@@ -100,21 +113,20 @@ def main():
     ap.add_argument("--versions", default="v2")
     ap.add_argument("--iters", type=int, default=15)
     args = ap.parse_args()
-    base_env = dict(os.environ)
     for name in args.configs.split(","):
         v1, v2, nbytes, S = build(name)
         for knob in args.knobs:
-            for k in list(os.environ):
-                if k.startswith("B200PA_") and k not in base_env:
-                    del os.environ[k]
+            for k, v in DEFAULTS.items():
+                ops.set_tuning(k, v)
             for kv in filter(None, knob.split(",")):
                 k, v = kv.split("=")
-                os.environ[k] = v
+                ops.set_tuning(k.strip().lower().replace("b200pa_", ""), int(v))
             for ver in args.versions.split(","):
                 fn = v1 if ver == "v1" else v2
-                med, best = timed(fn, args.iters)
-                print(f"{name:6s} {ver} [{knob or 'default':44s}] med {med:8.4f} ms best {best:8.4f} ms  "
-                      f"{nbytes / med / 1e6:7.0f} GB/s  tok/s {S / med * 1e3:10.0f}  "
+                med, best, b2b = timed(fn, args.iters)
+                print(f"{name:6s} {ver} [{knob or 'default':30s}] med {med:8.4f} ms best {best:8.4f} ms  "
+                      f"{nbytes / med / 1e6:7.0f} GB/s  b2b {b2b:8.4f} ms {nbytes / b2b / 1e6:7.0f} GB/s  "
+                      f"tok/s {S / med * 1e3:10.0f}  "
                       f"path={ops.last_attention_path()}/p{ops.last_attention_partitions()}", flush=True)
         del v1, v2
         torch.cuda.empty_cache()

@@ -178,3 +178,13 @@ def last_attention_path() -> str:
 
 def last_attention_partitions() -> int:
     return _C.last_attention_partitions()
+
+
+def prepare(device: int = 0) -> None:
+    """Allocate the per-device attention workspace now (optional; it is otherwise allocated by the first call)."""
+    _C.prepare(device)
+
+
+def set_tuning(key: str, value: int) -> None:
+    """Developer hook (tools/tune.py, tests): override a launch-tuning knob of libb200pa at run time."""
+    _C.set_tuning(key, value)

@@ -42,11 +42,43 @@ struct AttnKernelParams {
   int bs_vert_stride;
   int bs_block_size;
   int bs_head_sliding_step;
+  // persistent (stream-K) mma kernel only
+  int num_seqs;
+  int max_seq_len;          // caller's bound; sizes the grid, never trusted for correctness
+  float* sk_slots;          // per-device workspace: 2 partial-result slots per CTA
+  unsigned* sk_counters;    // per-device workspace: one self-resetting arrival counter per CTA
 };
+
+// Tuning knobs: read from the environment ONCE, when the library is first used (never on the
+// launch path), and adjustable afterwards only through b200pa_set_tuning() (developer tools).
+struct Tuning {
+  int stages = 0;           // B200PA_STAGES: TMA ring depth per warp (0 = table / deepest that fits)
+  int evict_normal = -1;    // B200PA_EVICT_NORMAL: -1 = table, 0 = evict_first, 1 = evict_normal
+  int force_simt = 0;       // B200PA_FORCE_SIMT: tests only — run the general SIMT family
+  int partition_size = 0;   // B200PA_PARTITION_SIZE: SIMT split size override (multiple of 512)
+  int max_partition = 4096; // B200PA_MAX_PARTITION: SIMT split size cap
+  int grid_ctas = 0;        // B200PA_GRID_CTAS: persistent kernel grid override (0 = SMs x occupancy)
+  int min_blocks_per_cta = 8;  // B200PA_MIN_BLOCKS_PER_CTA: small problems use fewer CTAs
+  int grid_kernel = 0;      // B200PA_GRID_KERNEL: A/B only — the round-1 one-CTA-per-(seq, KV head, split) kernel
+};
+Tuning& tuning();
+
+// Per-device workspace of the persistent kernel (allocated once per device, on first use).
+struct SkWorkspace {
+  float* slots = nullptr;
+  unsigned* counters = nullptr;
+  int max_ctas = 0;        // slots hold 2 x max_ctas partials of kSkMaxSlotBytes each
+  int num_sms = 0;
+};
+constexpr int kSkMaxSlotBytes = 32 * (2 * 16 * 4 + 4) * 4;  // head 256, 16 query heads per CTA
+int sk_workspace(int device, SkWorkspace* ws);  // B200PA_OK or a negative status
 
 // attention_mma.cu — returns B200PA_OK, or 1 when (dtype, kv, block, head) has no MMA
 // instantiation (caller falls through to the SIMT family), or a negative status.
 int launch_attention_mma(const AttnKernelParams& kp, int num_seqs, int dtype, int kv_dtype, cudaStream_t stream);
+// persistent stream-K variant (attention_sk_kernel.cuh); *grid_out = CTAs launched
+int launch_attention_sk(const AttnKernelParams& kp, int num_seqs, int dtype, int kv_dtype, cudaStream_t stream,
+                        int* grid_out);
 // Shared memory the mma kernel needs for (head_size, block_size, cache bytes, stages, g-tiles).
 size_t mma_smem_bytes(int head_size, int block_size, int cache_elem_bytes, int stages, int ng);
 

@@ -558,6 +558,14 @@ extern "C" int b200pa_get_max_shared_memory_per_block_device_attribute(int32_t d
   return v;
 }
 
+// csrc/cuda_utils_kernels.cu:5-15 (device_id < 0 = current device)
+extern "C" int b200pa_get_device_attribute(int32_t attribute, int32_t device_id) {
+  int device = device_id, v = 0;
+  if (device_id < 0 && cudaGetDevice(&device) != cudaSuccess) return -1;
+  if (cudaDeviceGetAttribute(&v, static_cast<cudaDeviceAttr>(attribute), device) != cudaSuccess) return -1;
+  return v;
+}
+
 extern "C" int b200pa_abi_version(void) { return B200PA_ABI_VERSION; }
 extern "C" int b200pa_last_cuda_error(void) { return g_last_cuda_error; }
 extern "C" const char* b200pa_last_attention_path(void) { return g_last_attention_path; }

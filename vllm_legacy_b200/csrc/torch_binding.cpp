@@ -379,6 +379,13 @@ int get_max_shared_memory_per_block_device_attribute(int device_id) {
   return v;
 }
 
+// csrc/cuda_utils.h / cuda_utils_kernels.cu:5-15
+int get_device_attribute(int attribute, int device_id) {
+  const int v = b200pa_get_device_attribute(attribute, device_id);
+  TORCH_CHECK(v >= 0, "cudaDeviceGetAttribute(", attribute, ") failed for device ", device_id);
+  return v;
+}
+
 // vllm/attention/ops/prefix_prefill.py:684-696 (context_attention_fwd), same argument order.  The
 // index tensors may be int32 (vLLM's metadata) or int64 (the reference's kernel test); int64 ones are
 // narrowed here.  scale = 1/sqrt(head_size) as the reference's wrapper fixes it (:706).
@@ -482,10 +489,16 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   cache_ops.def("convert_fp8", &convert_fp8, "Convert the key and value cache to fp8 data type");
   // csrc/pybind.cpp:87-95
   pybind11::module cuda_utils = m.def_submodule("cuda_utils", "vLLM cuda utils (B200)");
+  cuda_utils.def("get_device_attribute", &get_device_attribute, "Gets the specified device attribute.");
   cuda_utils.def("get_max_shared_memory_per_block_device_attribute", &get_max_shared_memory_per_block_device_attribute,
                  "Gets the maximum shared memory per block device attribute.");
   // diagnostics (not in the reference)
   m.def("last_attention_path", []() { return std::string(b200pa_last_attention_path()); });
   m.def("last_attention_partitions", []() { return b200pa_last_attention_partitions(); });
   m.def("abi_version", []() { return b200pa_abi_version(); });
+  m.def("prepare", [](int device) { check_status(b200pa_prepare(device), nullptr, torch::Tensor(), ""); },
+        "Allocate the per-device attention workspace now (e.g. before a CUDA-graph capture)");
+  m.def("set_tuning", [](const std::string& key, int value) {
+    TORCH_CHECK(b200pa_set_tuning(key.c_str(), value) == B200PA_OK, "b200pa: unknown tuning key ", key);
+  }, "Developer hook: override a tuning knob (tools/tune.py)");
 }
