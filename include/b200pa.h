@@ -315,7 +315,7 @@ int b200pa_get_device_attribute(int32_t attribute, int32_t device_id);
 /*
  * Attention workspace.  The persistent decode kernel cuts the flattened KV-block list of a launch
  * into equal ranges, one per resident CTA; an item cut by a range boundary leaves partial results
- * in a per-device workspace (2 slots per CTA + one arrival counter per CTA, ~10 MB), allocated by
+ * in a per-device workspace (2 slots per CTA + one arrival counter per CTA, 48 MB), allocated by
  * the first attention call on a device and kept for the life of the process.  b200pa_prepare()
  * allocates it explicitly (hosts that capture their very first call into a CUDA graph may prefer
  * that, although the lazy path is capture-safe too).  Attention calls on ONE device must not run
@@ -329,11 +329,20 @@ int b200pa_prepare(int32_t device);
  * min_blocks_per_cta, grid_kernel. */
 int b200pa_set_tuning(const char* key, int32_t value);
 
+/* Developer hook: device buffer of [grid][4] int64 that the persistent kernel fills with
+ * {smid, t_begin, t_end, blocks} per CTA (globaltimer ns); NULL (default) switches it off. */
+void b200pa_set_trace(void* device_buffer);
+
 /* Index arithmetic of the persistent kernel's work split (csrc/attention_sched.cuh), exported so
  * that the CPU test-suite exercises the very functions the kernel compiles. */
 int64_t b200pa_sched_range_begin(int64_t total_blocks, int32_t num_ctas, int32_t cta);
 int32_t b200pa_sched_cta_of(int64_t total_blocks, int32_t num_ctas, int64_t flat_index);
 int32_t b200pa_sched_effective_ctas(int64_t total_blocks, int32_t grid);
+
+/* Measurement aid (bench.py): read `bytes` of device memory once with streaming 128-bit loads — the
+ * read-only HBM stream rate a KV decode can be held against (MEASURED_PEAKS' figure is a read+write
+ * copy).  sink_u32: one device uint32 the kernel may increment. */
+int b200pa_read_stream_probe(const void* src, int64_t bytes, void* sink_u32, b200pa_stream_t stream);
 
 /* Diagnostics */
 int b200pa_abi_version(void);

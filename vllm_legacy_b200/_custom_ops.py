@@ -188,3 +188,8 @@ def prepare(device: int = 0) -> None:
 def set_tuning(key: str, value: int) -> None:
     """Developer hook (tools/tune.py, tests): override a launch-tuning knob of libb200pa at run time."""
     _C.set_tuning(key, value)
+
+
+def read_stream_probe(src: torch.Tensor, sink: torch.Tensor) -> None:
+    """Measurement aid (bench.py): read `src` once with streaming loads; `sink` is a 1-element int32 CUDA tensor."""
+    _C.read_stream_probe(src, sink)

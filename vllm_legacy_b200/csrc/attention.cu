@@ -44,9 +44,10 @@ static int alloc_workspace(int device, SkWorkspace* ws) {
   int sms = 0;
   B200PA_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
   ws->num_sms = sms;
-  ws->max_ctas = 2 * sms;
-  const size_t slot_bytes = (size_t)ws->max_ctas * 2 * kSkMaxSlotBytes;
-  const size_t counter_bytes = (size_t)ws->max_ctas * sizeof(unsigned);
+  ws->max_counters = kSkMaxCounters;
+  ws->slot_bytes = kSkWorkspaceSlotBytes;
+  const size_t slot_bytes = ws->slot_bytes;
+  const size_t counter_bytes = (size_t)ws->max_counters * sizeof(unsigned);
   // The first call may sit inside a stream capture (global mode forbids cudaMalloc): allocate in
   // relaxed mode and zero the counters on a private stream, so nothing is recorded in the graph.
   cudaStreamCaptureMode mode = cudaStreamCaptureModeRelaxed;
@@ -218,6 +219,11 @@ extern "C" int b200pa_paged_attention_v1(const b200pa_attn_params_t* p, b200pa_s
 extern "C" int b200pa_paged_attention_v2(const b200pa_attn_params_t* p, b200pa_stream_t stream) {
   return b200pa::run_attention(p, /*allow_split=*/true, stream);
 }
+
+namespace b200pa { long long* g_sk_trace = nullptr; }
+// Developer hook: device buffer of [grid][4] int64 the persistent kernel fills with {smid, t_begin, t_end, blocks}
+// per CTA (globaltimer ns); NULL switches the trace off.
+extern "C" void b200pa_set_trace(void* device_buffer) { b200pa::g_sk_trace = static_cast<long long*>(device_buffer); }
 
 // Allocate the per-device workspace of the persistent kernel now (e.g. before a CUDA-graph capture).
 extern "C" int b200pa_prepare(int32_t device) {

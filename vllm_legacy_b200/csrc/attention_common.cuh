@@ -47,6 +47,7 @@ struct AttnKernelParams {
   int max_seq_len;          // caller's bound; sizes the grid, never trusted for correctness
   float* sk_slots;          // per-device workspace: 2 partial-result slots per CTA
   unsigned* sk_counters;    // per-device workspace: one self-resetting arrival counter per CTA
+  long long* sk_trace;      // developer trace (b200pa_set_trace): [cta][4] = {smid, t_begin, t_end, blocks}, or null
 };
 
 // Tuning knobs: read from the environment ONCE, when the library is first used (never on the
@@ -67,10 +68,12 @@ Tuning& tuning();
 struct SkWorkspace {
   float* slots = nullptr;
   unsigned* counters = nullptr;
-  int max_ctas = 0;        // slots hold 2 x max_ctas partials of kSkMaxSlotBytes each
+  size_t slot_bytes = 0;   // bytes behind `slots`: 2 partials per CTA fit for grid <= slot_bytes / (2 * slot size)
+  int max_counters = 0;
   int num_sms = 0;
 };
-constexpr int kSkMaxSlotBytes = 32 * (2 * 16 * 4 + 4) * 4;  // head 256, 16 query heads per CTA
+constexpr size_t kSkWorkspaceSlotBytes = 48u << 20;
+constexpr int kSkMaxCounters = 16384;
 int sk_workspace(int device, SkWorkspace* ws);  // B200PA_OK or a negative status
 
 // attention_mma.cu — returns B200PA_OK, or 1 when (dtype, kv, block, head) has no MMA

@@ -10,6 +10,8 @@
 
 namespace b200pa {
 
+extern long long* g_sk_trace;
+
 constexpr int kSmemPerSM = 227 * 1024;       // usable shared memory per SM / max per CTA (opt-in)
 constexpr int kSmemReservedPerCta = 1024;    // system-reserved shared memory per resident CTA
 
@@ -101,12 +103,13 @@ static int launch_sk_one(AttnKernelParams kp, int num_seqs, cudaStream_t stream,
   if (rc != B200PA_OK) return rc;
   kp.sk_slots = ws.slots;
   kp.sk_counters = ws.counters;
+  kp.sk_trace = g_sk_trace;
   const int G = kp.num_heads / kp.num_kv_heads;
   const int q_tiles = (G + HPT - 1) / HPT;
   const int64_t upper = (int64_t)num_seqs * kp.num_kv_heads * q_tiles * std::max(1, (kp.max_seq_len + B - 1) / B);
   int64_t grid = tn.grid_ctas > 0 ? tn.grid_ctas : (int64_t)ws.num_sms * ctas_per_sm;
   grid = std::min<int64_t>(grid, std::max<int64_t>(1, upper / tn.min_blocks_per_cta));
-  grid = std::min<int64_t>(grid, ws.max_ctas);
+  grid = std::min<int64_t>(grid, std::min<int64_t>(ws.max_counters, ws.slot_bytes / (2 * sk_slot_floats(D, NG) * 4)));
   kernel<<<(unsigned)grid, kMmaThreads, smem, stream>>>(kp);
   B200PA_CUDA_CHECK(cudaGetLastError());
   if (grid_out) *grid_out = (int)grid;

@@ -124,6 +124,8 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
   const int Geff = sk_effective_ctas(W, (int)gridDim.x);
   const int cta = blockIdx.x;
   if (cta >= Geff) return;  // (whole CTA; also W == 0)
+  long long t_begin = 0;
+  if (p.sk_trace && threadIdx.x == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_begin));
   const long long f0 = sk_range_begin(W, Geff, cta);
   const int len = (int)(sk_range_begin(W, Geff, cta + 1) - f0);  // >= 1 blocks of this CTA
   {
@@ -617,6 +619,14 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
     if (last_item) break;
     next_item(cc);
     first_item = false;
+  }
+  if (p.sk_trace && threadIdx.x == 0) {
+    long long t_end;
+    unsigned smid;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_end));
+    asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+    long long* tr = p.sk_trace + (size_t)cta * 4;
+    tr[0] = smid; tr[1] = t_begin; tr[2] = t_end; tr[3] = len;
   }
 }
 

@@ -552,6 +552,45 @@ extern "C" int b200pa_convert_fp8(void* dst, const void* src, int64_t numel, int
   }
 }
 
+// ---- measurement aid: read-only HBM stream (bench.py's read-stream roofline denominator) ------------
+// MEASURED_PEAKS.json's hbm_gbs is a read+write copy; a KV decode is a pure read stream, which HBM3e
+// serves faster (no read/write turnarounds).  This kernel reads `bytes` once with 128-bit streaming
+// loads, 8 in flight per thread, and folds them into one word per CTA so nothing is optimised away.
+namespace b200pa {
+__global__ void __launch_bounds__(256) read_stream_probe_kernel(const int4* __restrict__ src, int64_t n_vec,
+                                                                 unsigned* __restrict__ sink) {
+  constexpr int U = 8;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned acc = 0;
+  for (; i + (U - 1) * stride < n_vec; i += U * stride) {
+    int4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = ld_nc_v4(src + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < U; ++u) acc ^= v[u].x ^ v[u].y ^ v[u].z ^ v[u].w;
+  }
+  for (; i < n_vec; i += stride) {
+    const int4 v = ld_nc_v4(src + i);
+    acc ^= v.x ^ v.y ^ v.z ^ v.w;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc ^= __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0 && acc == 0x9e3779b9u) atomicAdd(sink, 1u);  // practically never; keeps the loads live
+}
+}  // namespace b200pa
+
+extern "C" int b200pa_read_stream_probe(const void* src, int64_t bytes, void* sink_u32, b200pa_stream_t stream) {
+  if (!src || !sink_u32 || bytes < 16 || reinterpret_cast<uintptr_t>(src) % 16) return B200PA_ERR_INVALID_ARG;
+  int dev = 0, sms = 0;
+  B200PA_CUDA_CHECK(cudaGetDevice(&dev));
+  B200PA_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  b200pa::read_stream_probe_kernel<<<sms * 8, 256, 0, stream>>>(static_cast<const int4*>(src), bytes / 16,
+                                                                static_cast<unsigned*>(sink_u32));
+  B200PA_CUDA_CHECK(cudaGetLastError());
+  return B200PA_OK;
+}
+
 extern "C" int b200pa_get_max_shared_memory_per_block_device_attribute(int32_t device_id) {
   int v = 0;
   if (cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, device_id) != cudaSuccess) return -1;

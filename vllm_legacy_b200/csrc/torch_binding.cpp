@@ -496,6 +496,16 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("last_attention_path", []() { return std::string(b200pa_last_attention_path()); });
   m.def("last_attention_partitions", []() { return b200pa_last_attention_partitions(); });
   m.def("abi_version", []() { return b200pa_abi_version(); });
+  m.def("read_stream_probe", [](torch::Tensor& src, torch::Tensor& sink) {
+    TORCH_CHECK(src.is_cuda() && src.is_contiguous() && sink.is_cuda() && sink.numel() >= 1 && sink.element_size() == 4,
+                "read_stream_probe: contiguous CUDA tensor + a 4-byte CUDA sink");
+    const at::cuda::OptionalCUDAGuard device_guard(device_of(src));
+    check_status(b200pa_read_stream_probe(src.data_ptr(), src.numel() * src.element_size(), sink.data_ptr(),
+                                          current_stream()), nullptr, src, "");
+  }, "Measurement aid: stream a tensor once with read-only 128-bit loads");
+  m.def("set_trace", [](const c10::optional<torch::Tensor>& buf) {
+    b200pa_set_trace(buf.has_value() ? buf->data_ptr() : nullptr);
+  }, "Developer hook: int64 CUDA tensor [grid, 4] filled with {smid, t_begin, t_end, blocks} per CTA, or None");
   m.def("prepare", [](int device) { check_status(b200pa_prepare(device), nullptr, torch::Tensor(), ""); },
         "Allocate the per-device attention workspace now (e.g. before a CUDA-graph capture)");
   m.def("set_tuning", [](const std::string& key, int value) {
