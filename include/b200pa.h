@@ -326,7 +326,7 @@ int b200pa_prepare(int32_t device);
 /* Developer hook (tools/tune.py, tests): override a tuning knob at run time.  The same knobs are
  * read from the environment (B200PA_<KEY>) once, when the library is first used — never per call.
  * Keys: stages, evict_normal, force_simt, partition_size, max_partition, grid_ctas,
- * min_blocks_per_cta, grid_kernel. */
+ * min_blocks_per_cta, grid_kernel, pool_pct, chunks_per_cta, cs_min. */
 int b200pa_set_tuning(const char* key, int32_t value);
 
 /* Developer hook: device buffer of [grid][4] int64 that the persistent kernel fills with
@@ -338,6 +338,13 @@ void b200pa_set_trace(void* device_buffer);
 int64_t b200pa_sched_range_begin(int64_t total_blocks, int32_t num_ctas, int32_t cta);
 int32_t b200pa_sched_cta_of(int64_t total_blocks, int32_t num_ctas, int64_t flat_index);
 int32_t b200pa_sched_effective_ctas(int64_t total_blocks, int32_t grid);
+/* chunk list of a launch: out[0..4] = {static region size, static chunks, pool chunk size, pool chunks, all chunks} */
+void b200pa_sched_geometry(int64_t total_blocks, int32_t grid, int32_t pool_pct, int32_t chunks_per_cta,
+                           int32_t cs_min, int32_t max_chunks, int64_t* out);
+int64_t b200pa_sched_chunk_begin(int64_t total_blocks, int32_t grid, int32_t pool_pct, int32_t chunks_per_cta,
+                                 int32_t cs_min, int32_t max_chunks, int32_t chunk);
+int32_t b200pa_sched_chunk_of(int64_t total_blocks, int32_t grid, int32_t pool_pct, int32_t chunks_per_cta,
+                              int32_t cs_min, int32_t max_chunks, int64_t flat_index);
 
 /* Measurement aid (bench.py): read `bytes` of device memory once with streaming 128-bit loads — the
  * read-only HBM stream rate a KV decode can be held against (MEASURED_PEAKS' figure is a read+write

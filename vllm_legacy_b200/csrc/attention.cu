@@ -30,6 +30,9 @@ Tuning& tuning() {
     v.grid_ctas = env_int("B200PA_GRID_CTAS", v.grid_ctas);
     v.min_blocks_per_cta = std::max(1, env_int("B200PA_MIN_BLOCKS_PER_CTA", v.min_blocks_per_cta));
     v.grid_kernel = env_int("B200PA_GRID_KERNEL", v.grid_kernel);
+    v.pool_pct = std::min(100, std::max(0, env_int("B200PA_POOL_PCT", v.pool_pct)));
+    v.chunks_per_cta = std::max(1, env_int("B200PA_CHUNKS_PER_CTA", v.chunks_per_cta));
+    v.cs_min = std::max(1, env_int("B200PA_CS_MIN", v.cs_min));
     return v;
   }();
   return t;
@@ -47,7 +50,7 @@ static int alloc_workspace(int device, SkWorkspace* ws) {
   ws->max_counters = kSkMaxCounters;
   ws->slot_bytes = kSkWorkspaceSlotBytes;
   const size_t slot_bytes = ws->slot_bytes;
-  const size_t counter_bytes = (size_t)ws->max_counters * sizeof(unsigned);
+  const size_t counter_bytes = ((size_t)ws->max_counters + 2) * sizeof(unsigned);
   // The first call may sit inside a stream capture (global mode forbids cudaMalloc): allocate in
   // relaxed mode and zero the counters on a private stream, so nothing is recorded in the graph.
   cudaStreamCaptureMode mode = cudaStreamCaptureModeRelaxed;
@@ -70,6 +73,7 @@ static int alloc_workspace(int device, SkWorkspace* ws) {
   }
   ws->slots = reinterpret_cast<float*>(base);
   ws->counters = reinterpret_cast<unsigned*>(base + slot_bytes);
+  ws->pool = ws->counters + ws->max_counters;
   return B200PA_OK;
 }
 
@@ -239,7 +243,8 @@ extern "C" int b200pa_set_tuning(const char* key, int32_t value) {
   struct { const char* k; int* v; } map[] = {
       {"stages", &t.stages}, {"evict_normal", &t.evict_normal}, {"force_simt", &t.force_simt},
       {"partition_size", &t.partition_size}, {"max_partition", &t.max_partition}, {"grid_ctas", &t.grid_ctas},
-      {"min_blocks_per_cta", &t.min_blocks_per_cta}, {"grid_kernel", &t.grid_kernel}};
+      {"min_blocks_per_cta", &t.min_blocks_per_cta}, {"grid_kernel", &t.grid_kernel}, {"pool_pct", &t.pool_pct},
+      {"chunks_per_cta", &t.chunks_per_cta}, {"cs_min", &t.cs_min}};
   for (auto& m : map)
     if (std::strcmp(m.k, key) == 0) {
       *m.v = value;
@@ -252,3 +257,17 @@ extern "C" int b200pa_set_tuning(const char* key, int32_t value) {
 extern "C" int64_t b200pa_sched_range_begin(int64_t W, int32_t G, int32_t c) { return b200pa::sk_range_begin(W, G, c); }
 extern "C" int32_t b200pa_sched_cta_of(int64_t W, int32_t G, int64_t f) { return b200pa::sk_cta_of(W, G, f); }
 extern "C" int32_t b200pa_sched_effective_ctas(int64_t W, int32_t grid) { return b200pa::sk_effective_ctas(W, grid); }
+// geometry of the chunk list: out[0..4] = {W1, Gs, cs, PC, number of chunks}
+extern "C" void b200pa_sched_geometry(int64_t W, int32_t grid, int32_t pool_pct, int32_t chunks_per_cta, int32_t cs_min,
+                                      int32_t max_chunks, int64_t* out) {
+  const b200pa::SkGeom g = b200pa::sk_geometry(W, grid, pool_pct, chunks_per_cta, cs_min, max_chunks);
+  out[0] = g.W1; out[1] = g.Gs; out[2] = g.cs; out[3] = g.PC; out[4] = b200pa::sk_num_chunks(g);
+}
+extern "C" int64_t b200pa_sched_chunk_begin(int64_t W, int32_t grid, int32_t pool_pct, int32_t chunks_per_cta,
+                                            int32_t cs_min, int32_t max_chunks, int32_t chunk) {
+  return b200pa::sk_chunk_begin(b200pa::sk_geometry(W, grid, pool_pct, chunks_per_cta, cs_min, max_chunks), chunk);
+}
+extern "C" int32_t b200pa_sched_chunk_of(int64_t W, int32_t grid, int32_t pool_pct, int32_t chunks_per_cta,
+                                         int32_t cs_min, int32_t max_chunks, int64_t f) {
+  return b200pa::sk_chunk_of(b200pa::sk_geometry(W, grid, pool_pct, chunks_per_cta, cs_min, max_chunks), f);
+}

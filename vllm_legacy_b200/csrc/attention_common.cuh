@@ -47,6 +47,11 @@ struct AttnKernelParams {
   int max_seq_len;          // caller's bound; sizes the grid, never trusted for correctness
   float* sk_slots;          // per-device workspace: 2 partial-result slots per CTA
   unsigned* sk_counters;    // per-device workspace: one self-resetting arrival counter per CTA
+  unsigned* sk_pool;        // per-device workspace: [0] next pool chunk, [1] CTAs finished (both self-resetting)
+  int sk_max_chunks;        // workspace capacity in chunks (2 slots + 1 counter each)
+  int sk_pool_pct;          // share of the blocks handed out dynamically, percent
+  int sk_chunks_per_cta;    // pool chunks aimed at per CTA
+  int sk_cs_min;            // smallest pool chunk, blocks
   long long* sk_trace;      // developer trace (b200pa_set_trace): [cta][4] = {smid, t_begin, t_end, blocks}, or null
 };
 
@@ -60,6 +65,9 @@ struct Tuning {
   int max_partition = 4096; // B200PA_MAX_PARTITION: SIMT split size cap
   int grid_ctas = 0;        // B200PA_GRID_CTAS: persistent kernel grid override (0 = SMs x occupancy)
   int min_blocks_per_cta = 8;  // B200PA_MIN_BLOCKS_PER_CTA: small problems use fewer CTAs
+  int pool_pct = 25;        // B200PA_POOL_PCT: share of the KV blocks scheduled dynamically (0 = static split)
+  int chunks_per_cta = 8;   // B200PA_CHUNKS_PER_CTA: pool chunks per CTA aimed at (smaller chunks, smaller tail)
+  int cs_min = 8;           // B200PA_CS_MIN: smallest pool chunk in KV blocks
   int grid_kernel = 0;      // B200PA_GRID_KERNEL: A/B only — the round-1 one-CTA-per-(seq, KV head, split) kernel
 };
 Tuning& tuning();
@@ -68,6 +76,7 @@ Tuning& tuning();
 struct SkWorkspace {
   float* slots = nullptr;
   unsigned* counters = nullptr;
+  unsigned* pool = nullptr;  // [2], right behind the counters
   size_t slot_bytes = 0;   // bytes behind `slots`: 2 partials per CTA fit for grid <= slot_bytes / (2 * slot size)
   int max_counters = 0;
   int num_sms = 0;

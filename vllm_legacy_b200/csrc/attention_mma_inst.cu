@@ -59,20 +59,22 @@ static int launch_one(AttnKernelParams kp, int num_seqs, cudaStream_t stream) {
   return B200PA_OK;
 }
 
-// Persistent stream-K launch: one resident wave of CTAs (SMs x CTAs per SM), fewer for tiny problems.
+// Persistent launch: one resident wave of CTAs (SMs x CTAs per SM), fewer for tiny problems.
 template <typename T, int KV, int D, int B, int NG>
 static int launch_sk_one(AttnKernelParams kp, int num_seqs, cudaStream_t stream, int* grid_out) {
   constexpr int CTB = KV == B200PA_KV_AUTO ? 2 : 1;
   constexpr int STAGE = 2 * B * D * CTB;
   constexpr int HPT = 8 * NG;
-  constexpr bool kTwoCtas = (D * NG <= 256);
+  constexpr bool kTwoCtas = sk_two_ctas(D, NG);
   const Tuning& tn = tuning();
-  auto total_bytes = [&](int nst) { return kMmaWarps * nst * STAGE + sk_fixed_smem_bytes(D, NG) + kMmaWarps * nst * 8; };
+  // rings + merge buffers / part queue / flags + a full and an empty mbarrier per stage
+  auto total_bytes = [&](int nst) { return kMmaWarps * nst * STAGE + sk_fixed_smem_bytes(D, NG) + 2 * kMmaWarps * nst * 8; };
   const int full = kSmemPerSM - kSmemReservedPerCta, half = kSmemPerSM / 2 - kSmemReservedPerCta;
   int nst = tn.stages;
   if (nst <= 0) {
     // Deepest ring (<= 8 stages) that still lets two CTAs share an SM; if that is shallower than
-    // 3 stages (2 for the 16 KiB+ stages) take the whole SM for one CTA instead.
+    // 3 stages take the whole SM for one CTA instead.  Bytes in flight per SM are what hide the
+    // HBM latency: 2 CTAs x 4 warps x 3 stages x 8 KiB = 192 KiB for bf16 / D128 / B16.
     nst = 0;
     if (kTwoCtas)
       for (int n = 8; n >= 3 && nst == 0; --n)
@@ -103,14 +105,19 @@ static int launch_sk_one(AttnKernelParams kp, int num_seqs, cudaStream_t stream,
   if (rc != B200PA_OK) return rc;
   kp.sk_slots = ws.slots;
   kp.sk_counters = ws.counters;
+  kp.sk_pool = ws.pool;
+  kp.sk_max_chunks = (int)std::min<int64_t>(ws.max_counters, ws.slot_bytes / (2 * sk_slot_floats(D, NG) * 4));
+  kp.sk_pool_pct = tn.pool_pct;
+  kp.sk_chunks_per_cta = tn.chunks_per_cta;
+  kp.sk_cs_min = tn.cs_min;
   kp.sk_trace = g_sk_trace;
   const int G = kp.num_heads / kp.num_kv_heads;
   const int q_tiles = (G + HPT - 1) / HPT;
   const int64_t upper = (int64_t)num_seqs * kp.num_kv_heads * q_tiles * std::max(1, (kp.max_seq_len + B - 1) / B);
   int64_t grid = tn.grid_ctas > 0 ? tn.grid_ctas : (int64_t)ws.num_sms * ctas_per_sm;
   grid = std::min<int64_t>(grid, std::max<int64_t>(1, upper / tn.min_blocks_per_cta));
-  grid = std::min<int64_t>(grid, std::min<int64_t>(ws.max_counters, ws.slot_bytes / (2 * sk_slot_floats(D, NG) * 4)));
-  kernel<<<(unsigned)grid, kMmaThreads, smem, stream>>>(kp);
+  grid = std::min<int64_t>(grid, kp.sk_max_chunks / 2);
+  kernel<<<(unsigned)grid, kSkThreads, smem, stream>>>(kp);
   B200PA_CUDA_CHECK(cudaGetLastError());
   if (grid_out) *grid_out = (int)grid;
   return B200PA_OK;

@@ -1,21 +1,29 @@
-// Persistent ("stream-K") paged-attention decode kernel for B200 (sm_100a).
+// Persistent paged-attention decode kernel for B200 (sm_100a): warp-specialised producer /
+// consumers over a dynamically scheduled, flattened KV-block list.
 //
-// Same per-block math as the grid kernel it replaces (TMA bulk-copy staged KV blocks, mma.sync
+// Same per-block math as the round-1 grid kernel (TMA bulk-copy staged KV blocks, mma.sync
 // contractions over the whole GQA group, online softmax in registers — see the notes in
-// attention_mma_kernel.cuh), but the launch is ONE resident wave of CTAs and the work is the
-// flattened list of KV blocks of all (sequence, KV head) items, cut into equal contiguous ranges
-// (attention_sched.cuh):
+// attention_mma_kernel.cuh), but:
 //
-//   * every CTA streams the same number of blocks whatever the batch shape — no wave tail for
-//     mid-size shards (256 sequences x 1 KV head at TP8), no long-sequence stragglers in ragged
-//     batches, and a single sequence is spread over all SMs (v1 needs no caller scratch for that);
-//   * each warp's TMA ring runs ACROSS item boundaries: while the warps merge one item's partial
-//     results the copies of the next item's blocks are already in flight, so the bytes in flight
-//     per SM stay constant for the whole kernel (the grid kernel drained its ring at the end of
-//     every CTA — ~10 % of a 512 KiB CTA's life);
-//   * an item cut by a CTA boundary leaves un-normalised (max, sum, O) partials in a workspace slot
-//     (<= 2 per CTA); the last part to finish — found with a self-resetting arrival counter — merges
-//     the slots in a fixed order (deterministic) and writes the output row.  No second launch.
+//   * ONE resident wave of CTAs (SMs x CTAs/SM) streams the flattened list of KV blocks of all
+//     (sequence, KV head) items.  The list is cut into a fixed set of chunks (attention_sched.cuh):
+//     one big static chunk per CTA + a pool of small chunks taken with an atomic counter, so every
+//     SM streams at its own rate until the work is gone (B200's SMs differ by +-20 % on equal
+//     ranges) and the tail is one small chunk.  A single sequence is spread over all SMs; v1 needs
+//     no caller scratch for that.
+//   * warp 4 is the PRODUCER: it scans seq_lens, takes chunks, walks the items of a chunk,
+//     publishes one "part" descriptor per (item x chunk) intersection in a shared-memory queue,
+//     looks the blocks up in the block table (32 entries per coalesced load) and issues the two
+//     `cp.async.bulk` copies per block into the ring of the consumer warp that owns the block
+//     (blocks go round-robin to warps 0-3; full/empty mbarrier pair per stage).  It runs ahead of
+//     the consumers by the whole ring, ACROSS item and chunk boundaries, so the bytes in flight
+//     per SM stay constant for the life of the kernel.
+//   * warps 0-3 are CONSUMERS: wait for a stage, QK^T / softmax / PV on it, release it.  At the
+//     end of a part the four partial (max, sum, O) states are merged through shared memory
+//     ((2,3) -> (0,1), 1 -> 0; named barriers, no CTA-wide barrier) and warp 0 writes the output
+//     row — or, when the item is cut by a chunk boundary, an un-normalised partial into the
+//     chunk's workspace slot.  The last part of an item to finish (self-resetting arrival
+//     counter) merges all its slots in chunk order — deterministic — with all four warps.
 //
 // Math parity with the reference kernel (attention_kernels.cu:86-496) is unchanged: fp32 QK
 // accumulation, logit = scale*qk + alibi*(j - len + 1), P rounded to the 16-bit type before P.V,
@@ -27,8 +35,11 @@
 
 namespace b200pa {
 
-// named barriers of the intra-CTA merge tree (id 0 is __syncthreads)
-constexpr int kSkBarFullA = 1, kSkBarEmptyA = 2, kSkBarFullB = 3, kSkBarEmptyB = 4;
+constexpr int kSkThreads = kMmaThreads + 32;  // 4 consumer warps + 1 producer warp
+constexpr int kSkPartQueue = 64;              // part descriptors in flight (> 4 * max stages + 8, see producer)
+
+// named barriers (id 0 is __syncthreads): merge tree of the consumer warps + the fix-up decision
+constexpr int kSkBarFullA = 1, kSkBarEmptyA = 2, kSkBarFullB = 3, kSkBarEmptyB = 4, kSkBarFix = 5;
 
 __device__ __forceinline__ void named_bar_sync(int id, int count) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
@@ -41,15 +52,31 @@ __device__ __forceinline__ float ld_cg_f32(const float* p) {
   asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
   return v;
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_smem(uint32_t addr) {
+  int v;
+  asm volatile("ld.acquire.cta.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_smem(uint32_t addr, int v) {
+  asm volatile("st.release.cta.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
 
 // A partial result in "fragment layout": register i of lane l at [i * 32 + l]; registers are the
 // O^T accumulators (NG * D/16 * 4), then the running maxima (NG) and the quad-reduced sums (NG).
 __host__ __device__ constexpr int sk_slot_floats(int D, int NG) { return 32 * (NG * (D / 16) * 4 + 2 * NG); }
-// shared memory next to the rings: three merge buffers + 64 bytes of scan scratch
-__host__ __device__ constexpr int sk_fixed_smem_bytes(int D, int NG) { return 3 * sk_slot_floats(D, NG) * 4 + 64; }
+// shared memory next to the rings: three merge buffers, the part queue, 16 bytes of flags
+__host__ __device__ constexpr int sk_fixed_smem_bytes(int D, int NG) {
+  return 3 * sk_slot_floats(D, NG) * 4 + kSkPartQueue * 32 + 16;
+}
+
+// Two CTAs per SM when 2 x 160 threads fit the register file at this head size / group tile.
+__host__ __device__ constexpr bool sk_two_ctas(int D, int NG) { return NG == 1 && D <= 128; }
 
 template <typename T, int KV, int D, int B, int NG>
-__global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
+__global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
     paged_attention_sk_kernel(const __grid_constant__ AttnKernelParams p) {
   using MT = typename std::conditional<KV == B200PA_KV_AUTO, T, __half>::type;  // tensor-core input type
   constexpr bool FP8 = KV != B200PA_KV_AUTO;
@@ -81,139 +108,188 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
   const int HK = p.num_kv_heads * q_tiles;  // work units per sequence
   const int NST = p.num_stages;
   const int S = p.num_seqs;
+  const int cta = blockIdx.x;
 
-  // shared memory: [4 warps x NST stages][bufA0 | bufA1 | bufB][64 B scan scratch][4 x NST mbarriers]
-  const uint32_t stage_base = smem_u32(smem) + warp * NST * STAGE;
+  // shared memory: [4 warps x NST stages][bufA0 | bufA1 | bufB][part queue][flags][full bars][empty bars]
+  const uint32_t ring_base = smem_u32(smem);
   float* bufA = reinterpret_cast<float*>(smem + kMmaWarps * NST * STAGE);
   float* bufB = bufA + 2 * SLOT;
-  uint8_t* misc = reinterpret_cast<uint8_t*>(bufA + 3 * SLOT);
-  long long* scan_tot = reinterpret_cast<long long*>(misc);          // [4]
-  long long* start_info = reinterpret_cast<long long*>(misc + 32);   // [0] first sequence, [1] blocks before it
-  const uint32_t bar_base = smem_u32(misc + 64) + warp * NST * 8;
+  int4* pq = reinterpret_cast<int4*>(bufA + 3 * SLOT);                 // [kSkPartQueue][2]
+  int* flags = reinterpret_cast<int*>(pq + kSkPartQueue * 2);          // [0] parts published, [1] fix-up decision
+  const uint32_t tail_addr = smem_u32(flags);
+  const uint32_t full_base = smem_u32(flags + 4);
+  const uint32_t empty_base = full_base + kMmaWarps * NST * 8;
 
-  auto blocks_of = [](int len) { return len > 0 ? (len + B - 1) / B : 0; };
-
-  // ---- phase 0: where does this CTA's range start?  (block-count scan over seq_lens) ---------------
-  const int per = (S + kMmaThreads - 1) / kMmaThreads;
-  const int lo = min((int)threadIdx.x * per, S), hi = min(lo + per, S);
-  long long mine = 0;
-  for (int s = lo; s < hi; ++s) {
-    const int len = p.seq_lens[s];
-    mine += blocks_of(len);
-    if (len <= 0 && blockIdx.x == 0) {  // empty context => zeros (nobody else touches this row)
-      T* o = static_cast<T*>(p.out) + (int64_t)s * p.num_heads * D;
-      for (int i = 0; i < p.num_heads * D; ++i) o[i] = from_float<T>(0.f);
-    }
-  }
-  long long incl = mine;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const long long v = __shfl_up_sync(FULL, incl, o);
-    if (lane >= o) incl += v;
-  }
-  if (lane == 31) scan_tot[warp] = incl;
-  __syncthreads();
-  long long total = 0;
-#pragma unroll
-  for (int w2 = 0; w2 < kMmaWarps; ++w2) {
-    const long long t = scan_tot[w2];
-    if (w2 < warp) incl += t;
-    total += t;
-  }
-  const long long W = total * HK;
-  const int Geff = sk_effective_ctas(W, (int)gridDim.x);
-  const int cta = blockIdx.x;
-  if (cta >= Geff) return;  // (whole CTA; also W == 0)
-  long long t_begin = 0;
-  if (p.sk_trace && threadIdx.x == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_begin));
-  const long long f0 = sk_range_begin(W, Geff, cta);
-  const int len = (int)(sk_range_begin(W, Geff, cta + 1) - f0);  // >= 1 blocks of this CTA
-  {
-    const long long x = f0 / HK;  // the start in units of "blocks of one unit"
-    const long long excl = incl - mine;
-    if (x >= excl && x < incl) {  // exactly one thread: the one whose slice holds the start
-      long long N = excl;
-      int s = lo;
-      for (;; ++s) {
-        const int n = blocks_of(p.seq_lens[s]);
-        if (x < N + n) break;
-        N += n;
-      }
-      start_info[0] = s;
-      start_info[1] = N;
-    }
-  }
-  __syncthreads();
-
-  // ---- cursors over the item list -------------------------------------------------------------------
-  // `base` = position of the item's block 0 relative to f0 (negative when the item began earlier).
-  struct Cur {
-    int seq, hk, n, slen, base;
-  };
-  auto next_item = [&](Cur& c) {
-    c.base += c.n;
-    if (++c.hk == HK) {
-      c.hk = 0;
-      do {
-        ++c.seq;
-        c.slen = p.seq_lens[c.seq];
-        c.n = blocks_of(c.slen);
-      } while (c.n == 0 && c.seq + 1 < S);
-    }
-  };
-  Cur c0;
-  {
-    c0.seq = (int)start_info[0];
-    c0.slen = p.seq_lens[c0.seq];
-    c0.n = blocks_of(c0.slen);
-    const long long r0 = f0 - start_info[1] * HK;  // in [0, n * HK)
-    c0.hk = (int)(r0 / c0.n);
-    c0.base = -(int)(r0 - (long long)c0.hk * c0.n);
-  }
-
-  const char* kcache = static_cast<const char*>(p.k_cache);
-  const char* vcache = static_cast<const char*>(p.v_cache);
-  const int64_t head_stride_bytes = p.kv_head_stride * CTB;
-  const int64_t blk_stride_bytes = p.kv_block_stride * CTB;
-  uint64_t policy = 0;
-  if (lane == 0) policy = (p.flags & 1) ? l2_evict_normal_policy() : l2_evict_first_policy();
-  policy = __shfl_sync(FULL, policy, 0);
-
-  auto issue = [&](const Cur& c, int rel, int phys, uint32_t bar, uint32_t dst) {
-    (void)rel;
-    const int kvh = q_tiles == 1 ? c.hk : c.hk / q_tiles;
-    const int64_t off = (int64_t)kvh * head_stride_bytes + (int64_t)phys * blk_stride_bytes;
-    mbar_arrive_expect_tx(bar, STAGE);
-    tma_bulk_g2s(dst, kcache + off, CHUNK, bar, policy);
-    tma_bulk_g2s(dst + CHUNK, vcache + off, CHUNK, bar, policy);
-  };
-
-  // ---- pipeline prologue: lane i issues this warp's block i (positions warp + 4 i) ---------------
-  if (lane == 0) {
-    for (int s = 0; s < NST; ++s) mbar_init(bar_base + s * 8, 1);
+  if (threadIdx.x == kMmaThreads) {  // producer lane 0 sets the pipeline up
+    for (int i = 0; i < 2 * kMmaWarps * NST; ++i) mbar_init(full_base + i * 8, 1);
+    flags[0] = 0;
+    flags[1] = 0;
     fence_proxy_async_smem();
   }
-  __syncwarp();
-  {
-    const int lrel = warp + kMmaWarps * lane;
-    if (lane < NST && lrel < len) {
-      Cur lc = c0;
-      while (lrel >= lc.base + lc.n) next_item(lc);
-      const int phys = p.block_tables[(int64_t)lc.seq * p.max_blocks_per_seq + (lrel - lc.base)];
-      issue(lc, lrel, phys, bar_base + lane * 8, stage_base + lane * STAGE);
-    }
-    __syncwarp();
-  }
-  // producer state (warp-uniform): the NEXT block to issue, its item and its physical block number
-  Cur pc = c0;
-  int prel = warp + kMmaWarps * NST;
-  int pphys = 0;
-  auto prod_seek = [&]() {
-    while (prel >= pc.base + pc.n) next_item(pc);
-    pphys = p.block_tables[(int64_t)pc.seq * p.max_blocks_per_seq + (prel - pc.base)];
-  };
-  if (prel < len) prod_seek();
+  long long t_begin = 0;
+  if (p.sk_trace && threadIdx.x == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_begin));
+  __syncthreads();
 
+  if (warp == kMmaWarps) {
+    // =============================================== PRODUCER ===============================================
+    auto blocks_of = [](int len) { return len > 0 ? (len + B - 1) / B : 0; };
+    // ---- block-count scan over seq_lens: lane l owns the slice [lo, hi) -------------------------------------
+    const int per = (S + 31) / 32;
+    const int lo = min(lane * per, S), hi = min(lo + per, S);
+    long long mine = 0;
+    for (int s = lo; s < hi; ++s) {
+      const int len = p.seq_lens[s];
+      mine += blocks_of(len);
+      if (len <= 0 && cta == 0) {  // empty context => zeros (nobody else touches this row)
+        T* o = static_cast<T*>(p.out) + (int64_t)s * p.num_heads * D;
+        for (int i = 0; i < p.num_heads * D; ++i) o[i] = from_float<T>(0.f);
+      }
+    }
+    long long incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const long long v = __shfl_up_sync(FULL, incl, o);
+      if (lane >= o) incl += v;
+    }
+    const long long excl = incl - mine;
+    const long long W = __shfl_sync(FULL, incl, 31) * HK;
+    const SkGeom geo = sk_geometry(W, (int)gridDim.x, p.sk_pool_pct, p.sk_chunks_per_cta, p.sk_cs_min, p.sk_max_chunks);
+    const int NC = sk_num_chunks(geo);
+
+    // `base` = position of the item's block 0 relative to the chunk start (negative: the item began earlier)
+    struct Cur {
+      int seq, hk, n, slen, base;
+    };
+    auto next_item = [&](Cur& c) {
+      c.base += c.n;
+      if (++c.hk == HK) {
+        c.hk = 0;
+        do {
+          ++c.seq;
+          c.slen = p.seq_lens[c.seq];
+          c.n = blocks_of(c.slen);
+        } while (c.n == 0 && c.seq + 1 < S);
+      }
+    };
+    auto locate = [&](long long f, Cur& c) {  // all lanes; the result is warp-uniform
+      const long long x = f / HK;             // in units of "blocks of one unit"
+      const int src = __ffs(__ballot_sync(FULL, x >= excl && x < incl)) - 1;  // the slice that holds it
+      int s = 0;
+      long long N = 0;
+      if (lane == src) {
+        N = excl;
+        for (s = lo;; ++s) {
+          const int n = blocks_of(p.seq_lens[s]);
+          if (x < N + n) break;
+          N += n;
+        }
+      }
+      s = __shfl_sync(FULL, s, src);
+      N = __shfl_sync(FULL, N, src);
+      c.seq = s;
+      c.slen = p.seq_lens[s];
+      c.n = blocks_of(c.slen);
+      const long long r0 = f - N * HK;  // in [0, n * HK)
+      c.hk = (int)(r0 / c.n);
+      c.base = -(int)(r0 - (long long)c.hk * c.n);
+    };
+
+    const char* kcache = static_cast<const char*>(p.k_cache);
+    const char* vcache = static_cast<const char*>(p.v_cache);
+    const int64_t head_stride_bytes = p.kv_head_stride * CTB;
+    const int64_t blk_stride_bytes = p.kv_block_stride * CTB;
+    const uint64_t policy = (p.flags & 1) ? l2_evict_normal_policy() : l2_evict_first_policy();
+
+    int gpos = 0;       // blocks issued so far; block g goes to consumer warp g & 3 as its (g >> 2)-th block
+    int st = 0;         // ring stage of block index g >> 2
+    uint32_t ph = 0;    // parity of its use count
+    int npart = 0;      // parts published
+    int nxt = 0;        // (lane 0) next pool chunk, taken a little before the current chunk ends
+    int chunk = cta;
+    if (cta >= geo.Gs) {
+      if (lane == 0) nxt = geo.Gs + (int)atomicAdd(p.sk_pool, 1u);
+      chunk = __shfl_sync(FULL, nxt, 0);
+    }
+    while (chunk < NC) {
+      const long long f0c = sk_chunk_begin(geo, chunk);
+      const int lenc = (int)(sk_chunk_begin(geo, chunk + 1) - f0c);
+      bool have_next = false;
+      Cur cur;
+      locate(f0c, cur);
+      for (int rel = 0;;) {
+        // ---- one part: the blocks [jb, je) of item `cur` that lie in this chunk ------------------------------
+        const int jb = rel - cur.base;
+        const int je = min(cur.n, lenc - cur.base);
+        const int cnt = je - jb;
+        int slot = -1, chx = 0;
+        if (!(jb == 0 && je == cur.n)) {  // the item is cut: who else holds a part of it?
+          slot = sk_slot_index(chunk, jb > 0);
+          const long long a = f0c + cur.base;  // flat index of the item's block 0
+          const int ch = sk_chunk_of(geo, a), cl = sk_chunk_of(geo, a + cur.n - 1);
+          chx = ch | ((cl - ch) << 16);
+        }
+        if (lane == 0) {
+          int4* e = pq + (npart & (kSkPartQueue - 1)) * 2;
+          e[0] = make_int4(cur.seq, cur.hk, cur.slen, jb);
+          e[1] = make_int4(cnt, gpos, slot, chx);
+          st_release_smem(tail_addr, npart + 1);
+        }
+        ++npart;
+        const int kvh = q_tiles == 1 ? cur.hk : cur.hk / q_tiles;
+        const char* kb = kcache + (int64_t)kvh * head_stride_bytes;
+        const char* vb = vcache + (int64_t)kvh * head_stride_bytes;
+        const int* bt = p.block_tables + (int64_t)cur.seq * p.max_blocks_per_seq + jb;
+        for (int i0 = 0; i0 < cnt; i0 += 32) {
+          if (!have_next && lenc - (rel + i0) <= 64) {  // close to the end of the chunk: take the next one
+            if (lane == 0) nxt = geo.Gs + (int)atomicAdd(p.sk_pool, 1u);
+            have_next = true;
+          }
+          const int nb = min(32, cnt - i0);
+          const int phys_l = lane < nb ? bt[i0 + lane] : 0;
+          for (int t = 0; t < nb; ++t) {
+            const int64_t off = (int64_t)__shfl_sync(FULL, phys_l, t) * blk_stride_bytes;
+            const int slot_i = (gpos & 3) * NST + st;
+            // the consumer must have released the previous use of this stage (none for the first NST)
+            if (gpos >= kMmaWarps * NST) mbar_wait(empty_base + slot_i * 8, ph ^ 1);
+            if (lane == 0) {
+              const uint32_t bar = full_base + slot_i * 8, dst = ring_base + slot_i * STAGE;
+              fence_proxy_async_smem();
+              mbar_arrive_expect_tx(bar, STAGE);
+              tma_bulk_g2s(dst, kb + off, CHUNK, bar, policy);
+              tma_bulk_g2s(dst + CHUNK, vb + off, CHUNK, bar, policy);
+            }
+            ++gpos;
+            if ((gpos & 3) == 0 && ++st == NST) {
+              st = 0;
+              ph ^= 1;
+            }
+          }
+        }
+        rel += cnt;
+        if (rel >= lenc) break;
+        next_item(cur);
+      }
+      if (!have_next && lane == 0) nxt = geo.Gs + (int)atomicAdd(p.sk_pool, 1u);
+      chunk = __shfl_sync(FULL, nxt, 0);
+    }
+    if (lane == 0) {
+      // end of stream: a part with no blocks
+      int4* e = pq + (npart & (kSkPartQueue - 1)) * 2;
+      e[0] = make_int4(0, 0, 0, 0);
+      e[1] = make_int4(0, gpos, -1, 0);
+      st_release_smem(tail_addr, npart + 1);
+      // the last CTA to get here re-arms the pool counter for the next launch
+      __threadfence();
+      if (atomicAdd(p.sk_pool + 1, 1u) == gridDim.x - 1) {
+        __threadfence();
+        p.sk_pool[0] = 0u;
+        p.sk_pool[1] = 0u;
+      }
+    }
+    return;
+  }
+
+  // ================================================= CONSUMERS =================================================
   // ---- per-lane constant offsets (see attention_mma_kernel.cuh for the token permutation) ---------
   auto rot = [](int q) { return q * NP / 4; };
   auto tokmap = [&](int nt, int j) { return TPT * (j >> 1) + 2 * ((nt + rot(j >> 1)) % NP) + (j & 1); };
@@ -234,13 +310,25 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
 #pragma unroll
   for (int nt = 0; nt < NT; ++nt) tpos[nt] = TPT * tig + 2 * ((nt + rot(tig)) % NP);
 
+
   const float z_mult = (FP8 ? p.kv_scale : p.scale) * kLog2e;  // S_raw -> log2-domain logit
   const float out_scale = FP8 ? p.kv_scale : 1.f;
   const bool has_alibi = p.alibi_slopes != nullptr;
 
-  // ---- running state of the current item ----------------------------------------------------------
+  // ---- running state of the current part ----------------------------------------------------------
   float m_run[NG], l_run[NG];
   float oacc[NG][KS][4];
+  auto reset_state = [&]() {
+#pragma unroll
+    for (int r = 0; r < NG; ++r) {
+      m_run[r] = kNegBig;
+      l_run[r] = 0.f;
+#pragma unroll
+      for (int dt = 0; dt < KS; ++dt)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) oacc[r][dt][e] = 0.f;
+    }
+  };
 
   // fragment-layout store / merge of (m, l, O); `l_run` must already be quad-reduced
   auto store_frag = [&](float* buf) {
@@ -281,21 +369,49 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
   auto ld_smem = [](const float* q) { return *q; };
   auto ld_glob = [](const float* q) { return ld_cg_f32(q); };
 
-  // ---- consumer loop over items -----------------------------------------------------------------------
-  Cur cc = c0;
-  int crel = warp;  // position (relative to f0) of this warp's next block
+
+  // Merge the four warps' (m, l, O) into warp 0: (2,3) -> (0,1) through bufA, 1 -> 0 through bufB.
+  // A buffer is handed back ("empty") at the start of the NEXT merge, so no arrival is left dangling.
+  int merges = 0;
+  auto tree_merge = [&]() {
+    if (warp >= 2) {
+      if (merges) named_bar_sync(kSkBarEmptyA, 128);
+      store_frag(bufA + (warp - 2) * SLOT);
+      __threadfence_block();
+      named_bar_arrive(kSkBarFullA, 128);
+    } else {
+      if (merges) named_bar_arrive(kSkBarEmptyA, 128);
+      named_bar_sync(kSkBarFullA, 128);
+      merge_frag(bufA + warp * SLOT, ld_smem);
+      if (warp == 1) {
+        if (merges) named_bar_sync(kSkBarEmptyB, 64);
+        store_frag(bufB);
+        __threadfence_block();
+        named_bar_arrive(kSkBarFullB, 64);
+      } else {
+        if (merges) named_bar_arrive(kSkBarEmptyB, 64);
+        named_bar_sync(kSkBarFullB, 64);
+        merge_frag(bufB, ld_smem);
+      }
+    }
+    ++merges;
+  };
+
+  const uint32_t my_ring = ring_base + warp * NST * STAGE;
+  const uint32_t my_full = full_base + warp * NST * 8, my_empty = empty_base + warp * NST * 8;
   int stage = 0;
   uint32_t phase = 0;
-  bool first_item = true;
-  for (;;) {
-    const int seq = cc.seq;
-    const int seq_len = cc.slen;
-    const int kv_head = q_tiles == 1 ? cc.hk : cc.hk / q_tiles;
-    const int qt = cc.hk - kv_head * q_tiles;
-    const int jb = max(0, -cc.base);            // this CTA's part of the item: blocks [jb, je)
-    const int je = min(cc.n, len - cc.base);
-    const int part_end = cc.base + je;
-    const bool last_item = cc.base + cc.n >= len;
+  int traced_blocks = 0;
+  for (int pi = 0;; ++pi) {
+    while (ld_acquire_smem(tail_addr) <= pi) {
+    }
+    const int4 e0 = pq[(pi & (kSkPartQueue - 1)) * 2], e1 = pq[(pi & (kSkPartQueue - 1)) * 2 + 1];
+    const int seq = e0.x, hk = e0.y, seq_len = e0.z, jb = e0.w;
+    const int cnt = e1.x, gpos = e1.y, slot = e1.z, chx = e1.w;
+    if (cnt == 0) break;
+    traced_blocks += cnt;
+    const int kv_head = q_tiles == 1 ? hk : hk / q_tiles;
+    const int qt = hk - kv_head * q_tiles;
 
     // Q fragments (A operand of QK^T) of this item
     // 16-bit cache: k index of step ks <-> d = 16ks + {2tig, 2tig+1 | +8};
@@ -326,23 +442,16 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
         alibi_l2[r] = (has_alibi && valid) ? p.alibi_slopes[kv_head * G + hr] * kLog2e : 0.f;
       }
     }
-#pragma unroll
-    for (int r = 0; r < NG; ++r) {
-      m_run[r] = kNegBig;
-      l_run[r] = 0.f;
-#pragma unroll
-      for (int dt = 0; dt < KS; ++dt)
-#pragma unroll
-        for (int e = 0; e < 4; ++e) oacc[r][dt][e] = 0.f;
-    }
+    reset_state();
 
-    for (; crel < part_end; crel += kMmaWarps) {
-      const uint32_t bar = bar_base + stage * 8;
-      const uint32_t kb = stage_base + stage * STAGE;
+
+    // this warp's blocks of the part: i with (gpos + i) % 4 == warp
+    for (int i = (warp - gpos) & 3; i < cnt; i += kMmaWarps) {
+      const uint32_t kb = my_ring + stage * STAGE;
       const uint32_t vb = kb + CHUNK;
-      const int blk_tok0 = (crel - cc.base) * B;  // first token of this block
-      const int n_valid = seq_len - blk_tok0;     // >= 1; < B only in the last block
-      mbar_wait(bar, phase);
+      const int blk_tok0 = (jb + i) * B;       // first token of this block
+      const int n_valid = seq_len - blk_tok0;  // >= 1; < B only in the last block
+      mbar_wait(my_full + stage * 8, phase);
 
       // ================= S = Q K^T =================
       float sacc[NT][4];
@@ -521,104 +630,67 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
                           pp[r][2 * kk], pp[r][2 * kk + 1]);
       }
 
-      // ================= refill this stage with the producer's next block =================
+      // ================= hand the stage back to the producer =================
       __syncwarp();
-      if (prel < len) {
-        if (lane == 0) {
-          fence_proxy_async_smem();
-          issue(pc, prel, pphys, bar, kb);
-        }
-        prel += kMmaWarps;
-        if (prel < len) prod_seek();
-      }
+      if (lane == 0) mbar_arrive(my_empty + stage * 8);
       if (++stage == NST) {
         stage = 0;
         phase ^= 1;
       }
     }
 
-    // ---- merge the four warps' partial states of this item: (2,3) -> (0,1), 1 -> 0 -------------------
+    // ---- end of the part: merge the four warps' states; warp 0 owns the result ------------------------
 #pragma unroll
     for (int r = 0; r < NG; ++r) {
       l_run[r] += __shfl_xor_sync(FULL, l_run[r], 1);
       l_run[r] += __shfl_xor_sync(FULL, l_run[r], 2);
     }
-    if (warp >= 2) {
-      if (!first_item) named_bar_sync(kSkBarEmptyA, 128);
-      store_frag(bufA + (warp - 2) * SLOT);
-      __threadfence_block();
-      named_bar_arrive(kSkBarFullA, 128);
-    } else {
-      named_bar_sync(kSkBarFullA, 128);
-      merge_frag(bufA + warp * SLOT, ld_smem);
-      if (!last_item) named_bar_arrive(kSkBarEmptyA, 128);
-      if (warp == 1) {
-        if (!first_item) named_bar_sync(kSkBarEmptyB, 64);
-        store_frag(bufB);
-        __threadfence_block();
-        named_bar_arrive(kSkBarFullB, 64);
-      } else {
-        named_bar_sync(kSkBarFullB, 64);
-        merge_frag(bufB, ld_smem);
-        if (!last_item) named_bar_arrive(kSkBarEmptyB, 64);
+    tree_merge();
 
-        // ---- warp 0 owns the merged part: write the row, or leave a partial for the last arriver ----
-        auto write_out = [&]() {
+    auto write_out = [&]() {
 #pragma unroll
-          for (int r = 0; r < NG; ++r) {
-            const float l0 = __shfl_sync(FULL, l_run[r], 8 * tig), l1 = __shfl_sync(FULL, l_run[r], 8 * tig + 4);
-            const float inv0 = out_scale * __fdividef(1.f, l0 + 1e-6f);
-            const float inv1 = out_scale * __fdividef(1.f, l1 + 1e-6f);
-            const int hr0 = qt * HPT + 8 * r + 2 * tig;
-            T* o0 = static_cast<T*>(p.out) + ((int64_t)seq * p.num_heads + kv_head * G + hr0) * D + gid;
+      for (int r = 0; r < NG; ++r) {
+        const float l0 = __shfl_sync(FULL, l_run[r], 8 * tig), l1 = __shfl_sync(FULL, l_run[r], 8 * tig + 4);
+        const float inv0 = out_scale * __fdividef(1.f, l0 + 1e-6f);
+        const float inv1 = out_scale * __fdividef(1.f, l1 + 1e-6f);
+        const int hr0 = qt * HPT + 8 * r + 2 * tig;
+        T* o0 = static_cast<T*>(p.out) + ((int64_t)seq * p.num_heads + kv_head * G + hr0) * D + gid;
 #pragma unroll
-            for (int dt = 0; dt < KS; ++dt) {
-              if (hr0 < G) {
-                o0[16 * dt] = from_float<T>(oacc[r][dt][0] * inv0);
-                o0[16 * dt + 8] = from_float<T>(oacc[r][dt][2] * inv0);
-              }
-              if (hr0 + 1 < G) {
-                o0[D + 16 * dt] = from_float<T>(oacc[r][dt][1] * inv1);
-                o0[D + 16 * dt + 8] = from_float<T>(oacc[r][dt][3] * inv1);
-              }
-            }
+        for (int dt = 0; dt < KS; ++dt) {
+          if (hr0 < G) {
+            o0[16 * dt] = from_float<T>(oacc[r][dt][0] * inv0);
+            o0[16 * dt + 8] = from_float<T>(oacc[r][dt][2] * inv0);
           }
-        };
-        if (jb == 0 && je == cc.n) {
-          write_out();
-        } else {
-          float* slots = p.sk_slots;
-          store_frag(slots + (size_t)sk_slot_index(cta, jb > 0) * SLOT);
-          __threadfence();
-          __syncwarp();
-          const long long a = f0 + cc.base;  // flat index of the item's block 0
-          const int ch = sk_cta_of(W, Geff, a), cl = sk_cta_of(W, Geff, a + cc.n - 1);
-          int last = 0;
-          if (lane == 0) last = atomicAdd(p.sk_counters + ch, 1u) == (unsigned)(cl - ch);
-          last = __shfl_sync(FULL, last, 0);
-          if (last) {  // every part of the item is in its slot: merge them in CTA order
-            __threadfence();
-#pragma unroll
-            for (int r = 0; r < NG; ++r) {
-              m_run[r] = kNegBig;
-              l_run[r] = 0.f;
-#pragma unroll
-              for (int dt = 0; dt < KS; ++dt)
-#pragma unroll
-                for (int e = 0; e < 4; ++e) oacc[r][dt][e] = 0.f;
-            }
-            for (int c2 = ch; c2 <= cl; ++c2)
-              merge_frag(slots + (size_t)sk_slot_index(c2, c2 != ch) * SLOT, ld_glob);
-            write_out();
-            if (lane == 0) p.sk_counters[ch] = 0u;  // self-resetting: the next launch starts from zero
+          if (hr0 + 1 < G) {
+            o0[D + 16 * dt] = from_float<T>(oacc[r][dt][1] * inv1);
+            o0[D + 16 * dt + 8] = from_float<T>(oacc[r][dt][3] * inv1);
           }
         }
       }
+    };
+    if (slot < 0) {  // the whole item was in this chunk
+      if (warp == 0) write_out();
+      continue;
     }
-
-    if (last_item) break;
-    next_item(cc);
-    first_item = false;
+    // ---- the item is cut by a chunk boundary: leave the partial; the last part to arrive merges them all ----
+    const int ch = chx & 0xffff, span = chx >> 16;  // parts live in chunks ch .. ch + span
+    if (warp == 0) {
+      store_frag(p.sk_slots + (size_t)slot * SLOT);
+      __threadfence();
+      __syncwarp();
+      if (lane == 0) flags[1] = atomicAdd(p.sk_counters + ch, 1u) == (unsigned)span;
+    }
+    named_bar_sync(kSkBarFix, 128);  // (also publishes flags[1])
+    if (!*reinterpret_cast<volatile int*>(flags + 1)) continue;
+    __threadfence();
+    reset_state();
+    for (int c2 = ch + warp; c2 <= ch + span; c2 += kMmaWarps)
+      merge_frag(p.sk_slots + (size_t)sk_slot_index(c2, c2 != ch) * SLOT, ld_glob);
+    tree_merge();
+    if (warp == 0) {
+      write_out();
+      if (lane == 0) p.sk_counters[ch] = 0u;  // self-resetting: the next launch starts from zero
+    }
   }
   if (p.sk_trace && threadIdx.x == 0) {
     long long t_end;
@@ -626,7 +698,10 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_end));
     asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
     long long* tr = p.sk_trace + (size_t)cta * 4;
-    tr[0] = smid; tr[1] = t_begin; tr[2] = t_end; tr[3] = len;
+    tr[0] = smid;
+    tr[1] = t_begin;
+    tr[2] = t_end;
+    tr[3] = traced_blocks;
   }
 }
 
