@@ -66,8 +66,8 @@ struct Tuning {
   int grid_ctas = 0;        // B200PA_GRID_CTAS: persistent kernel grid override (0 = SMs x occupancy)
   int min_blocks_per_cta = 8;  // B200PA_MIN_BLOCKS_PER_CTA: small problems use fewer CTAs
   int pool_pct = 25;        // B200PA_POOL_PCT: share of the KV blocks scheduled dynamically (0 = static split)
-  int chunks_per_cta = 8;   // B200PA_CHUNKS_PER_CTA: pool chunks per CTA aimed at (smaller chunks, smaller tail)
-  int cs_min = 8;           // B200PA_CS_MIN: smallest pool chunk in KV blocks
+  int chunks_per_cta = 6;   // B200PA_CHUNKS_PER_CTA: pool chunks per CTA aimed at (smaller chunks, smaller tail)
+  int cs_min = 24;          // B200PA_CS_MIN: smallest pool chunk in KV blocks
   int grid_kernel = 0;      // B200PA_GRID_KERNEL: A/B only — the round-1 one-CTA-per-(seq, KV head, split) kernel
 };
 Tuning& tuning();

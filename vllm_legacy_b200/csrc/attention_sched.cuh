@@ -67,7 +67,9 @@ B200PA_HD SkGeom sk_geometry(int64_t W, int grid, int pool_pct, int chunks_per_c
   SkGeom g;
   g.W = W;
   int64_t pool = W * pool_pct / 100;
-  if (pool < cs_min) pool = 0;  // a few blocks: not worth a hand-off
+  // Small launches stay static: a pool chunk costs a part hand-off (queue entry, merge, workspace slot,
+  // arrival counter), which only pays when the static chunks are several pool chunks long.
+  if (W < (int64_t)grid * 6 * cs_min) pool = 0;
   g.W1 = W - pool;
   g.Gs = g.W1 > 0 ? sk_effective_ctas(g.W1, grid) : 0;
   int64_t cap = (int64_t)chunks_per_cta * grid;

@@ -200,9 +200,9 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
     const int64_t blk_stride_bytes = p.kv_block_stride * CTB;
     const uint64_t policy = (p.flags & 1) ? l2_evict_normal_policy() : l2_evict_first_policy();
 
-    int gpos = 0;       // blocks issued so far; block g goes to consumer warp g & 3 as its (g >> 2)-th block
-    int st = 0;         // ring stage of block index g >> 2
-    uint32_t ph = 0;    // parity of its use count
+    // Ring state of the four consumer warps, one byte each: bits 0-3 next stage, bit 4 parity of the
+    // stage's use count, bit 5 "every stage has been used once" (then the empty barrier must be waited).
+    uint32_t rings = 0;
     int npart = 0;      // parts published
     int nxt = 0;        // (lane 0) next pool chunk, taken a little before the current chunk ends
     int chunk = cta;
@@ -228,10 +228,14 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
           const int ch = sk_chunk_of(geo, a), cl = sk_chunk_of(geo, a + cur.n - 1);
           chx = ch | ((cl - ch) << 16);
         }
+        // Block i of the part goes to consumer warp (i + rot) & 3.  rot depends on the part only (not on what
+        // this CTA streamed before), so the grouping of the partial sums — hence every output bit — is the same
+        // whichever CTA takes the chunk; the seq + hk term spreads the first blocks of short items over the warps.
+        const int rot = (jb + cur.seq + cur.hk) & 3;
         if (lane == 0) {
           int4* e = pq + (npart & (kSkPartQueue - 1)) * 2;
           e[0] = make_int4(cur.seq, cur.hk, cur.slen, jb);
-          e[1] = make_int4(cnt, gpos, slot, chx);
+          e[1] = make_int4(cnt, rot, slot, chx);
           st_release_smem(tail_addr, npart + 1);
         }
         ++npart;
@@ -248,21 +252,20 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
           const int phys_l = lane < nb ? bt[i0 + lane] : 0;
           for (int t = 0; t < nb; ++t) {
             const int64_t off = (int64_t)__shfl_sync(FULL, phys_l, t) * blk_stride_bytes;
-            const int slot_i = (gpos & 3) * NST + st;
-            // the consumer must have released the previous use of this stage (none for the first NST)
-            if (gpos >= kMmaWarps * NST) mbar_wait(empty_base + slot_i * 8, ph ^ 1);
-            if (lane == 0) {
-              const uint32_t bar = full_base + slot_i * 8, dst = ring_base + slot_i * STAGE;
-              fence_proxy_async_smem();
-              mbar_arrive_expect_tx(bar, STAGE);
-              tma_bulk_g2s(dst, kb + off, CHUNK, bar, policy);
-              tma_bulk_g2s(dst + CHUNK, vb + off, CHUNK, bar, policy);
+            const int w = (i0 + t + rot) & 3;
+            const uint32_t rs = (rings >> (8 * w)) & 0xffu;
+            const int st = rs & 0xf;
+            const int slot_i = w * NST + st;
+            // the consumer must have released the previous use of this stage (none for the first NST blocks)
+            if (rs & 0x20u) mbar_wait(empty_base + slot_i * 8, ((rs >> 4) & 1u) ^ 1u);
+            if (lane < 2) {  // lane 0: K chunk (+ the transaction count), lane 1: V chunk — one issue slot
+              const uint32_t bar = full_base + slot_i * 8, dst = ring_base + slot_i * STAGE + lane * CHUNK;
+              if (lane == 0) mbar_arrive_expect_tx(bar, STAGE);
+              tma_bulk_g2s(dst, (lane ? vb : kb) + off, CHUNK, bar, policy);
             }
-            ++gpos;
-            if ((gpos & 3) == 0 && ++st == NST) {
-              st = 0;
-              ph ^= 1;
-            }
+            uint32_t nrs = rs + 1;
+            if ((int)(nrs & 0xf) == NST) nrs = ((nrs & 0x30u) ^ 0x10u) | 0x20u;
+            rings = (rings & ~(0xffu << (8 * w))) | (nrs << (8 * w));
           }
         }
         rel += cnt;
@@ -276,7 +279,7 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
       // end of stream: a part with no blocks
       int4* e = pq + (npart & (kSkPartQueue - 1)) * 2;
       e[0] = make_int4(0, 0, 0, 0);
-      e[1] = make_int4(0, gpos, -1, 0);
+      e[1] = make_int4(0, 0, -1, 0);
       st_release_smem(tail_addr, npart + 1);
       // the last CTA to get here re-arms the pool counter for the next launch
       __threadfence();
@@ -366,6 +369,45 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
       m_run[r] = M;
     }
   };
+  // Two workspace slots at once (all loads issued before the first use).
+  auto merge_frag2 = [&](const float* x, const float* y) {
+    float ox[NO + 3 * NG], oy[NO + 3 * NG];
+#pragma unroll
+    for (int r = 0; r < NG; ++r) {
+#pragma unroll
+      for (int i = 0; i < KS * 4; ++i) {
+        ox[r * KS * 4 + i] = ld_cg_f32(x + (r * KS * 4 + i) * 32 + lane);
+        oy[r * KS * 4 + i] = ld_cg_f32(y + (r * KS * 4 + i) * 32 + lane);
+      }
+      ox[NO + 3 * r] = ld_cg_f32(x + (NO + r) * 32 + 8 * tig);
+      ox[NO + 3 * r + 1] = ld_cg_f32(x + (NO + r) * 32 + 8 * tig + 4);
+      ox[NO + 3 * r + 2] = ld_cg_f32(x + (NO + r) * 32 + lane);
+      oy[NO + 3 * r] = ld_cg_f32(y + (NO + r) * 32 + 8 * tig);
+      oy[NO + 3 * r + 1] = ld_cg_f32(y + (NO + r) * 32 + 8 * tig + 4);
+      oy[NO + 3 * r + 2] = ld_cg_f32(y + (NO + r) * 32 + lane);
+    }
+#pragma unroll
+    for (int r = 0; r < NG; ++r) {
+      const float lx = ld_cg_f32(x + (NO + NG + r) * 32 + lane), ly = ld_cg_f32(y + (NO + NG + r) * 32 + lane);
+      const float ms0 = __shfl_sync(FULL, m_run[r], 8 * tig), ms1 = __shfl_sync(FULL, m_run[r], 8 * tig + 4);
+      const float M0 = fmaxf(ms0, fmaxf(ox[NO + 3 * r], oy[NO + 3 * r]));
+      const float M1 = fmaxf(ms1, fmaxf(ox[NO + 3 * r + 1], oy[NO + 3 * r + 1]));
+      const float fs0 = exp2f(ms0 - M0), fx0 = exp2f(ox[NO + 3 * r] - M0), fy0 = exp2f(oy[NO + 3 * r] - M0);
+      const float fs1 = exp2f(ms1 - M1), fx1 = exp2f(ox[NO + 3 * r + 1] - M1), fy1 = exp2f(oy[NO + 3 * r + 1] - M1);
+#pragma unroll
+      for (int dt = 0; dt < KS; ++dt) {
+        const int i = (r * KS + dt) * 4;
+        oacc[r][dt][0] = (oacc[r][dt][0] * fs0 + ox[i] * fx0) + oy[i] * fy0;
+        oacc[r][dt][1] = (oacc[r][dt][1] * fs1 + ox[i + 1] * fx1) + oy[i + 1] * fy1;
+        oacc[r][dt][2] = (oacc[r][dt][2] * fs0 + ox[i + 2] * fx0) + oy[i + 2] * fy0;
+        oacc[r][dt][3] = (oacc[r][dt][3] * fs1 + ox[i + 3] * fx1) + oy[i + 3] * fy1;
+      }
+      const float mx = ox[NO + 3 * r + 2], my = oy[NO + 3 * r + 2];
+      const float M = fmaxf(m_run[r], fmaxf(mx, my));
+      l_run[r] = (l_run[r] * exp2f(m_run[r] - M) + lx * exp2f(mx - M)) + ly * exp2f(my - M);
+      m_run[r] = M;
+    }
+  };
   auto ld_smem = [](const float* q) { return *q; };
   auto ld_glob = [](const float* q) { return ld_cg_f32(q); };
 
@@ -407,7 +449,7 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
     }
     const int4 e0 = pq[(pi & (kSkPartQueue - 1)) * 2], e1 = pq[(pi & (kSkPartQueue - 1)) * 2 + 1];
     const int seq = e0.x, hk = e0.y, seq_len = e0.z, jb = e0.w;
-    const int cnt = e1.x, gpos = e1.y, slot = e1.z, chx = e1.w;
+    const int cnt = e1.x, rot = e1.y, slot = e1.z, chx = e1.w;
     if (cnt == 0) break;
     traced_blocks += cnt;
     const int kv_head = q_tiles == 1 ? hk : hk / q_tiles;
@@ -445,8 +487,8 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
     reset_state();
 
 
-    // this warp's blocks of the part: i with (gpos + i) % 4 == warp
-    for (int i = (warp - gpos) & 3; i < cnt; i += kMmaWarps) {
+    // this warp's blocks of the part: i with (i + rot) % 4 == warp
+    for (int i = (warp - rot) & 3; i < cnt; i += kMmaWarps) {
       const uint32_t kb = my_ring + stage * STAGE;
       const uint32_t vb = kb + CHUNK;
       const int blk_tok0 = (jb + i) * B;       // first token of this block
@@ -674,19 +716,35 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
     }
     // ---- the item is cut by a chunk boundary: leave the partial; the last part to arrive merges them all ----
     const int ch = chx & 0xffff, span = chx >> 16;  // parts live in chunks ch .. ch + span
+    const bool coop = span >= 3;                    // many parts: all four warps merge (uniform: from the descriptor)
+    int last = 0;
     if (warp == 0) {
       store_frag(p.sk_slots + (size_t)slot * SLOT);
       __threadfence();
       __syncwarp();
-      if (lane == 0) flags[1] = atomicAdd(p.sk_counters + ch, 1u) == (unsigned)span;
+      if (lane == 0) last = atomicAdd(p.sk_counters + ch, 1u) == (unsigned)span;
+      last = __shfl_sync(FULL, last, 0);
+      if (coop && lane == 0) flags[1] = last;
     }
-    named_bar_sync(kSkBarFix, 128);  // (also publishes flags[1])
-    if (!*reinterpret_cast<volatile int*>(flags + 1)) continue;
+    if (coop) {
+      named_bar_sync(kSkBarFix, 128);  // (also publishes flags[1])
+      last = *reinterpret_cast<volatile int*>(flags + 1);
+    }
+    if (!last) continue;  // (warps 1-3 of a non-cooperative part always continue)
     __threadfence();
     reset_state();
-    for (int c2 = ch + warp; c2 <= ch + span; c2 += kMmaWarps)
-      merge_frag(p.sk_slots + (size_t)sk_slot_index(c2, c2 != ch) * SLOT, ld_glob);
-    tree_merge();
+    {
+      const int step = coop ? kMmaWarps : 1;
+      int c2 = ch + (coop ? warp : 0);
+      if constexpr (NO <= 32) {  // two slots per round: twice the loads in flight
+        for (; c2 + step <= ch + span; c2 += 2 * step)
+          merge_frag2(p.sk_slots + (size_t)sk_slot_index(c2, c2 != ch) * SLOT,
+                      p.sk_slots + (size_t)sk_slot_index(c2 + step, true) * SLOT);
+      }
+      for (; c2 <= ch + span; c2 += step)
+        merge_frag(p.sk_slots + (size_t)sk_slot_index(c2, c2 != ch) * SLOT, ld_glob);
+    }
+    if (coop) tree_merge();
     if (warp == 0) {
       write_out();
       if (lane == 0) p.sk_counters[ch] = 0u;  // self-resetting: the next launch starts from zero
