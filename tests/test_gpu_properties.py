@@ -161,7 +161,12 @@ def test_ragged_long_context_mix(ops, block_size):
     q_f = q.clone()
     q_f[3] = q_f[2]
     o = _attn(ops, "v1", q_f, kc, vc, Hkv, scale, bt_f, sl_f, block_size, L, "auto")
-    assert torch.equal(o[2].view(torch.int16), o[3].view(torch.int16))
+    # The persistent kernel cuts the flattened block list at positions that depend on where a sequence sits in the
+    # batch, so two rows with identical content may group their fp32 partial sums differently: equal up to the
+    # rounding of the bf16 output (1 ulp at |o| < 0.125 is 4.9e-4), and bit-identical from launch to launch.
+    assert torch.allclose(o[2].float(), o[3].float(), atol=5e-4, rtol=0)
+    o_again = _attn(ops, "v1", q_f, kc, vc, Hkv, scale, bt_f, sl_f, block_size, L, "auto")
+    assert torch.equal(o.view(torch.int16), o_again.view(torch.int16))
 
 
 @torch.inference_mode()

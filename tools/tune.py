@@ -41,7 +41,7 @@ CONFIGS = {
     "short": ([200] * 1024, 32, 8, 128, 16, "auto"),       # many short sequences: item switches dominate
 }
 DEFAULTS = {"stages": 0, "evict_normal": -1, "force_simt": 0, "partition_size": 0, "max_partition": 4096,
-            "grid_ctas": 0, "min_blocks_per_cta": 8, "grid_kernel": 0, "pool_pct": 25, "chunks_per_cta": 8, "cs_min": 8}
+            "grid_ctas": 0, "min_blocks_per_cta": 8, "grid_kernel": 0, "pool_pct": 25, "chunks_per_cta": 6, "cs_min": 24}
 
 
 def build(name):

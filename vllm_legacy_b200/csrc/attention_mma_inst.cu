@@ -67,8 +67,8 @@ static int launch_sk_one(AttnKernelParams kp, int num_seqs, cudaStream_t stream,
   constexpr int HPT = 8 * NG;
   constexpr bool kTwoCtas = sk_two_ctas(D, NG);
   const Tuning& tn = tuning();
-  // rings + merge buffers / part queue / flags + a full and an empty mbarrier per stage
-  auto total_bytes = [&](int nst) { return kMmaWarps * nst * STAGE + sk_fixed_smem_bytes(D, NG) + 2 * kMmaWarps * nst * 8; };
+  // rings + merge buffers / part queue / address queues / flags + one mbarrier per stage
+  auto total_bytes = [&](int nst) { return kMmaWarps * nst * STAGE + sk_fixed_smem_bytes(D, NG) + kMmaWarps * nst * 8; };
   const int full = kSmemPerSM - kSmemReservedPerCta, half = kSmemPerSM / 2 - kSmemReservedPerCta;
   int nst = tn.stages;
   if (nst <= 0) {

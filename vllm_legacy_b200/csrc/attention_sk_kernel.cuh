@@ -11,14 +11,17 @@
 //     SM streams at its own rate until the work is gone (B200's SMs differ by +-20 % on equal
 //     ranges) and the tail is one small chunk.  A single sequence is spread over all SMs; v1 needs
 //     no caller scratch for that.
-//   * warp 4 is the PRODUCER: it scans seq_lens, takes chunks, walks the items of a chunk,
+//   * warp 4 is the SCHEDULER: it scans seq_lens, takes chunks, walks the items of a chunk,
 //     publishes one "part" descriptor per (item x chunk) intersection in a shared-memory queue,
-//     looks the blocks up in the block table (32 entries per coalesced load) and issues the two
-//     `cp.async.bulk` copies per block into the ring of the consumer warp that owns the block
-//     (blocks go round-robin to warps 0-3; full/empty mbarrier pair per stage).  It runs ahead of
-//     the consumers by the whole ring, ACROSS item and chunk boundaries, so the bytes in flight
-//     per SM stay constant for the life of the kernel.
-//   * warps 0-3 are CONSUMERS: wait for a stage, QK^T / softmax / PV on it, release it.  At the
+//     looks the blocks up in the block table (32 entries per coalesced load, one lane per block)
+//     and appends each block's cache byte offset to the ADDRESS QUEUE of the consumer warp that
+//     owns it (blocks of a part go round-robin to warps 0-3).  It runs up to 32 blocks per warp
+//     ahead, across item and chunk boundaries, so its own latencies (atomics, block-table loads,
+//     64-bit divisions) are never seen by the memory pipeline.
+//   * warps 0-3 are CONSUMERS, each with its own TMA ring: lane 0 pops addresses and issues the
+//     two `cp.async.bulk` copies per block as soon as a stage is free — ACROSS item and chunk
+//     boundaries, so the bytes in flight per SM stay constant for the life of the kernel — then
+//     the warp waits for a stage and runs QK^T / softmax / PV on it.  At the
 //     end of a part the four partial (max, sum, O) states are merged through shared memory
 //     ((2,3) -> (0,1), 1 -> 0; named barriers, no CTA-wide barrier) and warp 0 writes the output
 //     row — or, when the item is cut by a chunk boundary, an un-normalised partial into the
@@ -36,7 +39,8 @@
 namespace b200pa {
 
 constexpr int kSkThreads = kMmaThreads + 32;  // 4 consumer warps + 1 producer warp
-constexpr int kSkPartQueue = 64;              // part descriptors in flight (> 4 * max stages + 8, see producer)
+constexpr int kSkPartQueue = 64;              // part descriptors in flight (scheduler waits for room)
+constexpr int kSkAddrQueue = 32;              // block addresses in flight per consumer warp
 
 // named barriers (id 0 is __syncthreads): merge tree of the consumer warps + the fix-up decision
 constexpr int kSkBarFullA = 1, kSkBarEmptyA = 2, kSkBarFullB = 3, kSkBarEmptyB = 4, kSkBarFix = 5;
@@ -67,10 +71,13 @@ __device__ __forceinline__ void st_release_smem(uint32_t addr, int v) {
 // A partial result in "fragment layout": register i of lane l at [i * 32 + l]; registers are the
 // O^T accumulators (NG * D/16 * 4), then the running maxima (NG) and the quad-reduced sums (NG).
 __host__ __device__ constexpr int sk_slot_floats(int D, int NG) { return 32 * (NG * (D / 16) * 4 + 2 * NG); }
-// shared memory next to the rings: three merge buffers, the part queue, 16 bytes of flags
+// shared memory next to the rings: three merge buffers, the part queue, four address queues, 64 bytes of flags
 __host__ __device__ constexpr int sk_fixed_smem_bytes(int D, int NG) {
-  return 3 * sk_slot_floats(D, NG) * 4 + kSkPartQueue * 32 + 16;
+  return 3 * sk_slot_floats(D, NG) * 4 + kSkPartQueue * 32 + kMmaWarps * kSkAddrQueue * 8 + 64;
 }
+// flags (ints): parts published | parts consumed | fix-up decision | scheduler done | addresses published [4] |
+// addresses taken [4]
+enum { kSkFlTail = 0, kSkFlHead = 1, kSkFlFix = 2, kSkFlDone = 3, kSkFlAvail = 4, kSkFlTaken = 8 };
 
 // Two CTAs per SM when 2 x 160 threads fit the register file at this head size / group tile.
 __host__ __device__ constexpr bool sk_two_ctas(int D, int NG) { return NG == 1 && D <= 128; }
@@ -110,20 +117,20 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
   const int S = p.num_seqs;
   const int cta = blockIdx.x;
 
-  // shared memory: [4 warps x NST stages][bufA0 | bufA1 | bufB][part queue][flags][full bars][empty bars]
+  // shared memory: [4 warps x NST stages][bufA0 | bufA1 | bufB][part queue][address queues][flags][full bars]
   const uint32_t ring_base = smem_u32(smem);
   float* bufA = reinterpret_cast<float*>(smem + kMmaWarps * NST * STAGE);
   float* bufB = bufA + 2 * SLOT;
-  int4* pq = reinterpret_cast<int4*>(bufA + 3 * SLOT);                 // [kSkPartQueue][2]
-  int* flags = reinterpret_cast<int*>(pq + kSkPartQueue * 2);          // [0] parts published, [1] fix-up decision
-  const uint32_t tail_addr = smem_u32(flags);
-  const uint32_t full_base = smem_u32(flags + 4);
-  const uint32_t empty_base = full_base + kMmaWarps * NST * 8;
+  int4* pq = reinterpret_cast<int4*>(bufA + 3 * SLOT);                         // [kSkPartQueue][2]
+  long long* aq = reinterpret_cast<long long*>(pq + kSkPartQueue * 2);         // [4][kSkAddrQueue]
+  int* flags = reinterpret_cast<int*>(aq + kMmaWarps * kSkAddrQueue);          // [16]
+  const uint32_t flags_addr = smem_u32(flags);
+  const uint32_t tail_addr = flags_addr + 4 * kSkFlTail;
+  const uint32_t full_base = flags_addr + 64;
 
-  if (threadIdx.x == kMmaThreads) {  // producer lane 0 sets the pipeline up
-    for (int i = 0; i < 2 * kMmaWarps * NST; ++i) mbar_init(full_base + i * 8, 1);
-    flags[0] = 0;
-    flags[1] = 0;
+  if (threadIdx.x == kMmaThreads) {  // scheduler lane 0 sets the pipeline up
+    for (int i = 0; i < kMmaWarps * NST; ++i) mbar_init(full_base + i * 8, 1);
+    for (int i = 0; i < 16; ++i) flags[i] = 0;
     fence_proxy_async_smem();
   }
   long long t_begin = 0;
@@ -131,7 +138,7 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
   __syncthreads();
 
   if (warp == kMmaWarps) {
-    // =============================================== PRODUCER ===============================================
+    // =============================================== SCHEDULER ===============================================
     auto blocks_of = [](int len) { return len > 0 ? (len + B - 1) / B : 0; };
     // ---- block-count scan over seq_lens: lane l owns the slice [lo, hi) -------------------------------------
     const int per = (S + 31) / 32;
@@ -194,16 +201,11 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
       c.base = -(int)(r0 - (long long)c.hk * c.n);
     };
 
-    const char* kcache = static_cast<const char*>(p.k_cache);
-    const char* vcache = static_cast<const char*>(p.v_cache);
     const int64_t head_stride_bytes = p.kv_head_stride * CTB;
     const int64_t blk_stride_bytes = p.kv_block_stride * CTB;
-    const uint64_t policy = (p.flags & 1) ? l2_evict_normal_policy() : l2_evict_first_policy();
 
-    // Ring state of the four consumer warps, one byte each: bits 0-3 next stage, bit 4 parity of the
-    // stage's use count, bit 5 "every stage has been used once" (then the empty barrier must be waited).
-    uint32_t rings = 0;
-    int npart = 0;      // parts published
+    int nq0 = 0, nq1 = 0, nq2 = 0, nq3 = 0;  // addresses appended to the queue of consumer warp 0..3
+    int npart = 0;                           // parts published
     int nxt = 0;        // (lane 0) next pool chunk, taken a little before the current chunk ends
     int chunk = cta;
     if (cta >= geo.Gs) {
@@ -233,6 +235,9 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
         // whichever CTA takes the chunk; the seq + hk term spreads the first blocks of short items over the warps.
         const int rot = (jb + cur.seq + cur.hk) & 3;
         if (lane == 0) {
+          // room in the part queue?  (the consumers are within two parts of each other)
+          while (npart - ld_acquire_smem(flags_addr + 4 * kSkFlHead) > kSkPartQueue - 8) {
+          }
           int4* e = pq + (npart & (kSkPartQueue - 1)) * 2;
           e[0] = make_int4(cur.seq, cur.hk, cur.slen, jb);
           e[1] = make_int4(cnt, rot, slot, chx);
@@ -240,8 +245,7 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
         }
         ++npart;
         const int kvh = q_tiles == 1 ? cur.hk : cur.hk / q_tiles;
-        const char* kb = kcache + (int64_t)kvh * head_stride_bytes;
-        const char* vb = vcache + (int64_t)kvh * head_stride_bytes;
+        const int64_t head_off = (int64_t)kvh * head_stride_bytes;
         const int* bt = p.block_tables + (int64_t)cur.seq * p.max_blocks_per_seq + jb;
         for (int i0 = 0; i0 < cnt; i0 += 32) {
           if (!have_next && lenc - (rel + i0) <= 64) {  // close to the end of the chunk: take the next one
@@ -249,23 +253,27 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
             have_next = true;
           }
           const int nb = min(32, cnt - i0);
-          const int phys_l = lane < nb ? bt[i0 + lane] : 0;
-          for (int t = 0; t < nb; ++t) {
-            const int64_t off = (int64_t)__shfl_sync(FULL, phys_l, t) * blk_stride_bytes;
-            const int w = (i0 + t + rot) & 3;
-            const uint32_t rs = (rings >> (8 * w)) & 0xffu;
-            const int st = rs & 0xf;
-            const int slot_i = w * NST + st;
-            // the consumer must have released the previous use of this stage (none for the first NST blocks)
-            if (rs & 0x20u) mbar_wait(empty_base + slot_i * 8, ((rs >> 4) & 1u) ^ 1u);
-            if (lane < 2) {  // lane 0: K chunk (+ the transaction count), lane 1: V chunk — one issue slot
-              const uint32_t bar = full_base + slot_i * 8, dst = ring_base + slot_i * STAGE + lane * CHUNK;
-              if (lane == 0) mbar_arrive_expect_tx(bar, STAGE);
-              tma_bulk_g2s(dst, (lane ? vb : kb) + off, CHUNK, bar, policy);
+          // lane t owns block i0 + t of the part; lanes t, t + 4, ... feed the same consumer warp
+          const int64_t off = head_off + (lane < nb ? (int64_t)bt[i0 + lane] * blk_stride_bytes : 0);
+          const int w = (i0 + lane + rot) & 3;
+          const int first = (w - i0 - rot) & 3;                  // the first lane of this batch that feeds warp w
+          const int nw = nb > first ? (nb - first + 3) >> 2 : 0;  // blocks of this batch for warp w
+          const int base = w == 0 ? nq0 : w == 1 ? nq1 : w == 2 ? nq2 : nq3;
+          if (lane < kMmaWarps && nw > 0) {  // (lanes 0-3 feed four different warps) room in that warp's queue?
+            while (base + nw - ld_acquire_smem(flags_addr + 4 * (kSkFlTaken + w)) > kSkAddrQueue) {
             }
-            uint32_t nrs = rs + 1;
-            if ((int)(nrs & 0xf) == NST) nrs = ((nrs & 0x30u) ^ 0x10u) | 0x20u;
-            rings = (rings & ~(0xffu << (8 * w))) | (nrs << (8 * w));
+          }
+          __syncwarp();
+          if (lane < nb) aq[w * kSkAddrQueue + ((base + ((lane - first) >> 2)) & (kSkAddrQueue - 1))] = off;
+          __syncwarp();
+          if (lane < kMmaWarps && nw > 0) st_release_smem(flags_addr + 4 * (kSkFlAvail + w), base + nw);
+          // every lane advances all four counters
+          {
+            const int f0_ = (0 - i0 - rot) & 3, f1_ = (1 - i0 - rot) & 3, f2_ = (2 - i0 - rot) & 3, f3_ = (3 - i0 - rot) & 3;
+            nq0 += nb > f0_ ? (nb - f0_ + 3) >> 2 : 0;
+            nq1 += nb > f1_ ? (nb - f1_ + 3) >> 2 : 0;
+            nq2 += nb > f2_ ? (nb - f2_ + 3) >> 2 : 0;
+            nq3 += nb > f3_ ? (nb - f3_ + 3) >> 2 : 0;
           }
         }
         rel += cnt;
@@ -277,10 +285,13 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
     }
     if (lane == 0) {
       // end of stream: a part with no blocks
+      while (npart - ld_acquire_smem(flags_addr + 4 * kSkFlHead) > kSkPartQueue - 8) {
+      }
       int4* e = pq + (npart & (kSkPartQueue - 1)) * 2;
       e[0] = make_int4(0, 0, 0, 0);
       e[1] = make_int4(0, 0, -1, 0);
       st_release_smem(tail_addr, npart + 1);
+      st_release_smem(flags_addr + 4 * kSkFlDone, 1);
       // the last CTA to get here re-arms the pool counter for the next launch
       __threadfence();
       if (atomicAdd(p.sk_pool + 1, 1u) == gridDim.x - 1) {
@@ -439,18 +450,56 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
     ++merges;
   };
 
+  // ---- this warp's TMA ring: lane 0 pops block addresses from the warp's queue and issues the copies ----------
   const uint32_t my_ring = ring_base + warp * NST * STAGE;
-  const uint32_t my_full = full_base + warp * NST * 8, my_empty = empty_base + warp * NST * 8;
+  const uint32_t my_full = full_base + warp * NST * 8;
+  const long long* my_aq = aq + warp * kSkAddrQueue;
+  const uint32_t avail_addr = flags_addr + 4 * (kSkFlAvail + warp), taken_addr = flags_addr + 4 * (kSkFlTaken + warp);
+  const char* kcache = static_cast<const char*>(p.k_cache);
+  const char* vcache = static_cast<const char*>(p.v_cache);
+  uint64_t policy = 0;
+  if (lane == 0) policy = (p.flags & 1) ? l2_evict_normal_policy() : l2_evict_first_policy();
+  int consumed = 0;           // blocks this warp has finished
+  int issued = 0, istage = 0;  // (lane 0) blocks whose copies were issued; the stage the next one goes to
+  // Issue every block whose address is there and whose stage is free (non-blocking unless `need`: then block
+  // until block `consumed` itself has been issued — its part is published, so its address is on the way).
+  auto top_up = [&](bool need) {
+    if (lane == 0) {
+      for (;;) {
+        if (issued >= consumed + NST) break;  // ring full
+        int av = ld_acquire_smem(avail_addr);
+        if (av <= issued) {
+          if (!need || issued > consumed) break;
+          continue;  // spin: the scheduler is about to publish it
+        }
+        const int take = min(av, consumed + NST);
+        fence_proxy_async_smem();  // the stages below were read through the generic proxy
+        for (; issued < take; ++issued) {
+          const long long off = my_aq[issued & (kSkAddrQueue - 1)];
+          const uint32_t bar = my_full + istage * 8, dst = my_ring + istage * STAGE;
+          mbar_arrive_expect_tx(bar, STAGE);
+          tma_bulk_g2s(dst, kcache + off, CHUNK, bar, policy);
+          tma_bulk_g2s(dst + CHUNK, vcache + off, CHUNK, bar, policy);
+          if (++istage == NST) istage = 0;
+        }
+        st_release_smem(taken_addr, issued);
+      }
+    }
+    __syncwarp();
+  };
+
   int stage = 0;
   uint32_t phase = 0;
   int traced_blocks = 0;
   for (int pi = 0;; ++pi) {
+    top_up(false);
     while (ld_acquire_smem(tail_addr) <= pi) {
     }
     const int4 e0 = pq[(pi & (kSkPartQueue - 1)) * 2], e1 = pq[(pi & (kSkPartQueue - 1)) * 2 + 1];
     const int seq = e0.x, hk = e0.y, seq_len = e0.z, jb = e0.w;
     const int cnt = e1.x, rot = e1.y, slot = e1.z, chx = e1.w;
     if (cnt == 0) break;
+    if (threadIdx.x == 0) st_release_smem(flags_addr + 4 * kSkFlHead, pi + 1);
     traced_blocks += cnt;
     const int kv_head = q_tiles == 1 ? hk : hk / q_tiles;
     const int qt = hk - kv_head * q_tiles;
@@ -493,6 +542,7 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
       const uint32_t vb = kb + CHUNK;
       const int blk_tok0 = (jb + i) * B;       // first token of this block
       const int n_valid = seq_len - blk_tok0;  // >= 1; < B only in the last block
+      top_up(true);
       mbar_wait(my_full + stage * 8, phase);
 
       // ================= S = Q K^T =================
@@ -672,9 +722,10 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
                           pp[r][2 * kk], pp[r][2 * kk + 1]);
       }
 
-      // ================= hand the stage back to the producer =================
+      // ================= the stage is free: refill it with the next block of this warp's stream =================
       __syncwarp();
-      if (lane == 0) mbar_arrive(my_empty + stage * 8);
+      ++consumed;
+      top_up(false);
       if (++stage == NST) {
         stage = 0;
         phase ^= 1;
@@ -724,11 +775,11 @@ __global__ void __launch_bounds__(kSkThreads, sk_two_ctas(D, NG) ? 2 : 1)
       __syncwarp();
       if (lane == 0) last = atomicAdd(p.sk_counters + ch, 1u) == (unsigned)span;
       last = __shfl_sync(FULL, last, 0);
-      if (coop && lane == 0) flags[1] = last;
+      if (coop && lane == 0) flags[kSkFlFix] = last;
     }
     if (coop) {
-      named_bar_sync(kSkBarFix, 128);  // (also publishes flags[1])
-      last = *reinterpret_cast<volatile int*>(flags + 1);
+      named_bar_sync(kSkBarFix, 128);  // (also publishes the decision)
+      last = *reinterpret_cast<volatile int*>(flags + kSkFlFix);
     }
     if (!last) continue;  // (warps 1-3 of a non-cooperative part always continue)
     __threadfence();
