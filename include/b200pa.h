@@ -313,38 +313,22 @@ int b200pa_get_max_shared_memory_per_block_device_attribute(int32_t device_id);
 int b200pa_get_device_attribute(int32_t attribute, int32_t device_id);
 
 /*
- * Attention workspace.  The persistent decode kernel cuts the flattened KV-block list of a launch
- * into equal ranges, one per resident CTA; an item cut by a range boundary leaves partial results
- * in a per-device workspace (2 slots per CTA + one arrival counter per CTA, 48 MB), allocated by
- * the first attention call on a device and kept for the life of the process.  b200pa_prepare()
- * allocates it explicitly (hosts that capture their very first call into a CUDA graph may prefer
- * that, although the lazy path is capture-safe too).  Attention calls on ONE device must not run
- * concurrently on different streams (the reference's worker issues them on one stream).
+ * Attention workspace.  The tensor-core decode kernel splits long contexts over several CTAs and
+ * fuses the split-K reduce into the same launch (the last split of a (sequence, KV head) to finish
+ * merges them).  That needs one arrival counter per (sequence, KV head) — and, for
+ * paged_attention_v1 whose ABI carries no scratch, somewhere to keep the partial results — in a
+ * per-device workspace (64 MB scratch + 4 MB counters), allocated by the first attention call on a
+ * device and kept for the life of the process.  b200pa_prepare() allocates it explicitly (hosts
+ * that capture their very first call into a CUDA graph may prefer that, although the lazy path is
+ * capture-safe too).  Attention calls on ONE device must not run concurrently on different streams
+ * (the reference's worker issues them on one stream).
  */
 int b200pa_prepare(int32_t device);
 
 /* Developer hook (tools/tune.py, tests): override a tuning knob at run time.  The same knobs are
  * read from the environment (B200PA_<KEY>) once, when the library is first used — never per call.
- * Keys: stages, evict_normal, force_simt, partition_size, max_partition, grid_ctas,
- * min_blocks_per_cta, grid_kernel, pool_pct, chunks_per_cta, cs_min. */
+ * Keys: stages, evict_normal, force_simt, partition_size, max_partition, ctas_per_sm_target. */
 int b200pa_set_tuning(const char* key, int32_t value);
-
-/* Developer hook: device buffer of [grid][4] int64 that the persistent kernel fills with
- * {smid, t_begin, t_end, blocks} per CTA (globaltimer ns); NULL (default) switches it off. */
-void b200pa_set_trace(void* device_buffer);
-
-/* Index arithmetic of the persistent kernel's work split (csrc/attention_sched.cuh), exported so
- * that the CPU test-suite exercises the very functions the kernel compiles. */
-int64_t b200pa_sched_range_begin(int64_t total_blocks, int32_t num_ctas, int32_t cta);
-int32_t b200pa_sched_cta_of(int64_t total_blocks, int32_t num_ctas, int64_t flat_index);
-int32_t b200pa_sched_effective_ctas(int64_t total_blocks, int32_t grid);
-/* chunk list of a launch: out[0..4] = {static region size, static chunks, pool chunk size, pool chunks, all chunks} */
-void b200pa_sched_geometry(int64_t total_blocks, int32_t grid, int32_t pool_pct, int32_t chunks_per_cta,
-                           int32_t cs_min, int32_t max_chunks, int64_t* out);
-int64_t b200pa_sched_chunk_begin(int64_t total_blocks, int32_t grid, int32_t pool_pct, int32_t chunks_per_cta,
-                                 int32_t cs_min, int32_t max_chunks, int32_t chunk);
-int32_t b200pa_sched_chunk_of(int64_t total_blocks, int32_t grid, int32_t pool_pct, int32_t chunks_per_cta,
-                              int32_t cs_min, int32_t max_chunks, int64_t flat_index);
 
 /* Measurement aid (bench.py): read `bytes` of device memory once with streaming 128-bit loads — the
  * read-only HBM stream rate a KV decode can be held against (MEASURED_PEAKS' figure is a read+write
@@ -356,8 +340,7 @@ int b200pa_abi_version(void);
 const char* b200pa_status_string(int status);
 int b200pa_last_cuda_error(void); /* cudaError_t of the last B200PA_ERR_CUDA on this thread */
 /* Name of the kernel family the last attention call on this thread dispatched
- * to ("mma_tma" | "simt"), and the split it used (persistent kernel: CTAs launched;
- * SIMT family: context partitions); for tests and the bench. */
+ * to ("mma_tma" | "simt"), and the number of context splits it used; for tests and the bench. */
 const char* b200pa_last_attention_path(void);
 int b200pa_last_attention_partitions(void);
 

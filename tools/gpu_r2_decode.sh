@@ -1,5 +1,5 @@
 #!/bin/bash
-# GPU-box script (round 2): parity of the persistent decode kernel + A/B against the round-1 grid kernel.
+# GPU-box script (round 2): parity of the decode kernel with the fused split-K reduce + timing on every config.
 set -x
 cd "${GRAFT_REPO_ROOT:-/root/repo}"
 mkdir -p gpurun_out
@@ -7,7 +7,5 @@ mkdir -p gpurun_out
 tail -n 15 gpurun_out/pytest_attn.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "exit=$?" >> gpurun_out/smoke.log
 tail -n 3 gpurun_out/smoke.log
-timeout 600 python tools/sk_trace.py c2 c3tp8 > gpurun_out/sk_trace.log 2>&1; echo "exit=$?" >> gpurun_out/sk_trace.log
-cat gpurun_out/sk_trace.log
-timeout 1200 python tools/tune.py --configs c2,c3tp8,c3tp4,c3tp2,c1,c4,c5b16,c5b32,small,one,mid,short --versions v2 --knobs "" "pool_pct=0" "pool_pct=40" "chunks_per_cta=16" "chunks_per_cta=4" "grid_kernel=1" > gpurun_out/tune_ab.log 2>&1; echo "exit=$?" >> gpurun_out/tune_ab.log
+timeout 1200 python tools/tune.py --configs c2,c3tp8,c3tp4,c3tp2,c1,c4,c5b16,c5b32,small,one,mid,short --versions v1,v2 --knobs "" "ctas_per_sm_target=4" "ctas_per_sm_target=16" "stages=2" > gpurun_out/tune_ab.log 2>&1; echo "exit=$?" >> gpurun_out/tune_ab.log
 cat gpurun_out/tune_ab.log

@@ -1,7 +1,8 @@
 // C-ABI entry points b200pa_paged_attention_v1 / _v2 (include/b200pa.h): argument checks with
-// the reference's error classes, launch planning, dispatch to the persistent TMA + mma.sync
-// kernel or the general SIMT family (+ its split-K reduce), the per-device workspace of the
-// persistent kernel, and the tuning knobs (environment read once, never on the launch path).
+// the reference's error classes, launch planning (context splits sized for 148 SMs), dispatch to
+// the TMA + mma.sync family (split-K reduce fused into the kernel) or the general SIMT family
+// (+ its reduce kernel), the per-device workspace, and the tuning knobs (environment read once,
+// never on the launch path).
 //
 // Reference host side: csrc/attention/attention_kernels.cu:690-825 (v1), :844-1014 (v2).
 #include <algorithm>
@@ -10,7 +11,6 @@
 #include <mutex>
 
 #include "attention_common.cuh"
-#include "attention_sched.cuh"
 
 namespace b200pa {
 
@@ -27,30 +27,24 @@ Tuning& tuning() {
     v.force_simt = env_int("B200PA_FORCE_SIMT", v.force_simt);
     v.partition_size = env_int("B200PA_PARTITION_SIZE", v.partition_size);
     v.max_partition = env_int("B200PA_MAX_PARTITION", v.max_partition);
-    v.grid_ctas = env_int("B200PA_GRID_CTAS", v.grid_ctas);
-    v.min_blocks_per_cta = std::max(1, env_int("B200PA_MIN_BLOCKS_PER_CTA", v.min_blocks_per_cta));
-    v.grid_kernel = env_int("B200PA_GRID_KERNEL", v.grid_kernel);
-    v.pool_pct = std::min(100, std::max(0, env_int("B200PA_POOL_PCT", v.pool_pct)));
-    v.chunks_per_cta = std::max(1, env_int("B200PA_CHUNKS_PER_CTA", v.chunks_per_cta));
-    v.cs_min = std::max(1, env_int("B200PA_CS_MIN", v.cs_min));
+    v.ctas_per_sm_target = std::max(1, env_int("B200PA_CTAS_PER_SM_TARGET", v.ctas_per_sm_target));
     return v;
   }();
   return t;
 }
 
-// ---- per-device workspace of the persistent kernel -------------------------------------------------
-// 2 partial-result slots per resident CTA + one arrival counter per CTA (~10 MB per device),
-// allocated on the first attention call on a device (or by b200pa_prepare()) and kept for the
-// life of the process.  Calls on one device must not overlap in time on different streams (they
-// never do in the reference's worker: one stream, one step at a time).
-static int alloc_workspace(int device, SkWorkspace* ws) {
+// ---- per-device workspace -----------------------------------------------------------------------------
+// Arrival counters of the fused split-K reduce (4 MB) + the scratch paged_attention_v1 splits through
+// (64 MB; v2 uses the caller's exp_sums / max_logits / tmp_out).  Allocated by the first attention call on
+// a device (or by b200pa_prepare()) and kept for the life of the process.  Calls on one device must not
+// overlap in time on different streams (they never do in the reference's worker: one stream, one step).
+static int alloc_workspace(int device, AttnWorkspace* ws) {
   int sms = 0;
   B200PA_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
   ws->num_sms = sms;
-  ws->max_counters = kSkMaxCounters;
-  ws->slot_bytes = kSkWorkspaceSlotBytes;
-  const size_t slot_bytes = ws->slot_bytes;
-  const size_t counter_bytes = ((size_t)ws->max_counters + 2) * sizeof(unsigned);
+  ws->max_counters = kWorkspaceCounters;
+  ws->scratch_bytes = kWorkspaceScratchBytes;
+  const size_t counter_bytes = (size_t)ws->max_counters * sizeof(unsigned);
   // The first call may sit inside a stream capture (global mode forbids cudaMalloc): allocate in
   // relaxed mode and zero the counters on a private stream, so nothing is recorded in the graph.
   cudaStreamCaptureMode mode = cudaStreamCaptureModeRelaxed;
@@ -60,9 +54,9 @@ static int alloc_workspace(int device, SkWorkspace* ws) {
   if (e == cudaSuccess) e = cudaSetDevice(device);
   char* base = nullptr;
   cudaStream_t s = nullptr;
-  if (e == cudaSuccess) e = cudaMalloc(&base, slot_bytes + counter_bytes);
+  if (e == cudaSuccess) e = cudaMalloc(&base, ws->scratch_bytes + counter_bytes);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking);
-  if (e == cudaSuccess) e = cudaMemsetAsync(base + slot_bytes, 0, counter_bytes, s);
+  if (e == cudaSuccess) e = cudaMemsetAsync(base + ws->scratch_bytes, 0, counter_bytes, s);
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   if (s) cudaStreamDestroy(s);
   cudaSetDevice(prev);
@@ -71,19 +65,18 @@ static int alloc_workspace(int device, SkWorkspace* ws) {
     g_last_cuda_error = static_cast<int>(e);
     return B200PA_ERR_CUDA;
   }
-  ws->slots = reinterpret_cast<float*>(base);
-  ws->counters = reinterpret_cast<unsigned*>(base + slot_bytes);
-  ws->pool = ws->counters + ws->max_counters;
+  ws->scratch = base;
+  ws->counters = reinterpret_cast<unsigned*>(base + ws->scratch_bytes);
   return B200PA_OK;
 }
 
-int sk_workspace(int device, SkWorkspace* out) {
+int attn_workspace(int device, AttnWorkspace* out) {
   constexpr int kMaxDevices = 64;
-  static SkWorkspace table[kMaxDevices];
+  static AttnWorkspace table[kMaxDevices];
   static std::mutex mu;
   if (device < 0 || device >= kMaxDevices) return B200PA_ERR_INVALID_ARG;
   std::lock_guard<std::mutex> lock(mu);
-  if (!table[device].slots) {
+  if (!table[device].scratch) {
     const int rc = alloc_workspace(device, &table[device]);
     if (rc != B200PA_OK) return rc;
   }
@@ -99,9 +92,10 @@ static bool block_size_supported(int b) {  // attention_kernels.cu:789-803
 }
 
 constexpr int kRefPartition = 512;  // granularity the callers size the v2 scratch with
-constexpr int kNumSMs = 148;
 
-static int run_attention(const b200pa_attn_params_t* a, bool allow_split, cudaStream_t stream) {
+static int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+static int run_attention(const b200pa_attn_params_t* a, bool is_v2, cudaStream_t stream) {
   if (!a) return B200PA_ERR_INVALID_ARG;
   if (a->kv_dtype != B200PA_KV_AUTO && a->kv_dtype != B200PA_KV_FP8_E4M3 && a->kv_dtype != B200PA_KV_FP8_E5M2)
     return B200PA_ERR_KV_DTYPE;
@@ -114,7 +108,10 @@ static int run_attention(const b200pa_attn_params_t* a, bool allow_split, cudaSt
   if (a->num_seqs == 0) return B200PA_OK;
   if (!a->out || !a->query || !a->key_cache || !a->value_cache || !a->block_tables || !a->seq_lens)
     return B200PA_ERR_INVALID_ARG;
-  const int cache_bytes = a->kv_dtype == B200PA_KV_AUTO ? (a->dtype == B200PA_F32 ? 4 : 2) : 1;
+  if (is_v2 && (!a->exp_sums || !a->max_logits || !a->tmp_out || a->max_num_partitions <= 0))
+    return B200PA_ERR_INVALID_ARG;
+  const int elem = a->dtype == B200PA_F32 ? 4 : 2;
+  const int cache_bytes = a->kv_dtype == B200PA_KV_AUTO ? elem : 1;
   // 16-byte granularity of the paged layout (x = 16 / sizeof(cache_t)): the reference's vector
   // loads assume it too (attention_kernels.cu:200, 272-290).
   if (reinterpret_cast<uintptr_t>(a->key_cache) % 16 || reinterpret_cast<uintptr_t>(a->value_cache) % 16 ||
@@ -123,9 +120,6 @@ static int run_attention(const b200pa_attn_params_t* a, bool allow_split, cudaSt
 
   AttnKernelParams kp{};
   kp.out = a->out;
-  kp.exp_sums = a->exp_sums;
-  kp.max_logits = a->max_logits;
-  kp.tmp_out = a->tmp_out;
   kp.q = a->query;
   kp.k_cache = a->key_cache;
   kp.v_cache = a->value_cache;
@@ -147,8 +141,6 @@ static int run_attention(const b200pa_attn_params_t* a, bool allow_split, cudaSt
   kp.bs_vert_stride = a->blocksparse_vert_stride;
   kp.bs_block_size = a->blocksparse_block_size;
   kp.bs_head_sliding_step = a->blocksparse_head_sliding_step;
-  kp.num_seqs = a->num_seqs;
-  kp.max_seq_len = a->max_seq_len;
   const Tuning& tn = tuning();
   kp.num_stages = tn.stages;
   kp.flags = tn.evict_normal > 0 ? 1 : 0;
@@ -156,59 +148,86 @@ static int run_attention(const b200pa_attn_params_t* a, bool allow_split, cudaSt
   const bool blocksparse = a->blocksparse_vert_stride > 1;
   if (blocksparse && (a->blocksparse_block_size <= 0 || a->blocksparse_block_size % a->block_size != 0))
     return B200PA_ERR_INVALID_ARG;
-  const bool mma_ok = !blocksparse && a->dtype != B200PA_F32 && a->block_size != 8 &&
-                      tn.force_simt == 0;
+  // TMA + mma.sync family: 16-bit queries, block size 16 / 32, dense, 4-byte aligned query rows
+  const bool mma_ok = !blocksparse && a->dtype != B200PA_F32 && a->block_size != 8 && tn.force_simt == 0 &&
+                      reinterpret_cast<uintptr_t>(a->query) % 4 == 0 && a->q_stride % 2 == 0;
 
-  // ---- persistent TMA + mma.sync kernel: one launch, stream-K split over the resident CTAs --------
-  // (v1 and v2 are the same launch: the split needs no caller scratch, so v2's exp_sums /
-  // max_logits / tmp_out stay untouched.)
-  int rc = 1;
-  if (mma_ok && !tn.grid_kernel) {
-    int grid = 0;
-    rc = launch_attention_sk(kp, a->num_seqs, a->dtype, a->kv_dtype, stream, &grid);
-    if (rc == B200PA_OK) {
-      g_last_attention_path = "mma_tma";
-      g_last_attention_partitions = grid;
-      return B200PA_OK;
-    }
-    if (rc != 1) return rc;
+  // ---- split plan -----------------------------------------------------------------------
+  // One CTA streams the KV of one (sequence, KV head[, split]) for the whole GQA group (mma family)
+  // or of one (sequence, query head[, split]) (SIMT family).  The context is split when those units
+  // alone cannot give every SM several CTAs.  Splits are multiples of the reference's 512-token
+  // partition, so that v2's caller-sized scratch (ceil(max_seq_len/512) slots) always fits.
+  //   * mma family: v1 and v2 split alike.  v2 keeps its partials in the caller's scratch, v1 (whose ABI
+  //     has none) in the per-device workspace; the reduce is fused into the kernel (the last split of a
+  //     (sequence, KV head) to finish merges them), so both are ONE launch.
+  //   * SIMT family: v2 only, with the separate reduce kernel.
+  AttnWorkspace ws;
+  if (mma_ok) {
+    int dev = 0;
+    B200PA_CUDA_CHECK(cudaGetDevice(&dev));
+    const int rc = attn_workspace(dev, &ws);
+    if (rc != B200PA_OK) return rc;
   }
-
-  // ---- split plan of the grid kernels (general SIMT family) ----------------------------------------
-  // One CTA streams the KV of one (sequence, query head[, split]).  Split the context when those
-  // units alone cannot give every SM several CTAs; never below the reference's 512-token
-  // partition so the caller-sized scratch (ceil(max_seq_len/512) slots) always fits.
   kp.num_parts = 1;
   kp.partition_size = std::max(a->max_seq_len, 1);
-  kp.scratch_parts = std::max(a->max_num_partitions, 1);
-  const bool grid_mma = mma_ok && tn.grid_kernel;
-  if (allow_split) {
-    if (!a->exp_sums || !a->max_logits || !a->tmp_out || a->max_num_partitions <= 0) return B200PA_ERR_INVALID_ARG;
-    const int64_t units = (int64_t)a->num_seqs * (grid_mma ? a->num_kv_heads : a->num_heads);
-    const int64_t target = (int64_t)kNumSMs * 8;
-    int want = (int)std::min<int64_t>((target + units - 1) / units, a->max_num_partitions);
-    int psize = (a->max_seq_len + want - 1) / std::max(want, 1);
+  kp.scratch_parts = 1;
+  const int hpt = (a->num_heads / a->num_kv_heads) <= 8 ? 8 : 16;
+  const int q_tiles = mma_ok ? (a->num_heads / a->num_kv_heads + hpt - 1) / hpt : 1;
+  const int64_t units = (int64_t)a->num_seqs * (mma_ok ? a->num_kv_heads * q_tiles : a->num_heads);
+  const bool may_split = mma_ok ? units <= ws.max_counters : is_v2;
+  if (may_split && a->max_seq_len > kRefPartition) {
+    const int64_t target = (int64_t)(mma_ok ? ws.num_sms : 148) * tn.ctas_per_sm_target;
+    const int want = (int)std::max<int64_t>(1, (target + units - 1) / units);
+    int psize = (a->max_seq_len + want - 1) / want;
     psize = std::min(psize, tn.max_partition);
-    psize = (psize + kRefPartition - 1) / kRefPartition * kRefPartition;
-    const int forced = tn.partition_size;
-    if (forced > 0) psize = (forced + kRefPartition - 1) / kRefPartition * kRefPartition;
+    if (tn.partition_size > 0) psize = tn.partition_size;
+    psize = round_up(std::max(psize, 1), kRefPartition);
+    if (mma_ok) psize = std::max(psize, round_up((a->max_seq_len + kMmaMaxSplits - 1) / kMmaMaxSplits, kRefPartition));
+    if (mma_ok && !is_v2) {
+      // v1: the partials must fit the workspace — [S, Hq, parts, D] T + 2 x [S, Hq, parts] float
+      const int64_t per_part = (int64_t)a->num_seqs * a->num_heads * ((int64_t)a->head_size * elem + 8);
+      const int64_t max_parts = std::max<int64_t>(1, (int64_t)ws.scratch_bytes / std::max<int64_t>(per_part, 1));
+      psize = std::max(psize, round_up((int)((a->max_seq_len + max_parts - 1) / max_parts), kRefPartition));
+    }
     const int parts = (a->max_seq_len + psize - 1) / psize;
     if (parts > 1) {
-      kp.num_parts = parts;  // parts <= max_num_partitions because psize >= 512
+      kp.num_parts = parts;  // v2: parts <= max_num_partitions because psize is a multiple of 512
       kp.partition_size = psize;
     }
   }
+  if (kp.num_parts > 1) {
+    if (is_v2) {
+      kp.exp_sums = a->exp_sums;
+      kp.max_logits = a->max_logits;
+      kp.tmp_out = a->tmp_out;
+      kp.scratch_parts = a->max_num_partitions;
+    } else {
+      const int64_t rows = (int64_t)a->num_seqs * a->num_heads * kp.num_parts;
+      kp.tmp_out = ws.scratch;
+      kp.max_logits = reinterpret_cast<float*>(ws.scratch + rows * a->head_size * elem);
+      kp.exp_sums = kp.max_logits + rows;
+      kp.scratch_parts = kp.num_parts;
+    }
+    kp.sk_counters = ws.counters;
+  }
 
-  rc = 1;
-  if (grid_mma) {
+  int rc = 1;
+  if (mma_ok) {
     rc = launch_attention_mma(kp, a->num_seqs, a->dtype, a->kv_dtype, stream);
-    if (rc == B200PA_OK) g_last_attention_path = "mma_grid";
+    if (rc == B200PA_OK) {
+      g_last_attention_path = "mma_tma";
+      g_last_attention_partitions = kp.num_parts;
+      return B200PA_OK;  // (the reduce is part of the kernel)
+    }
+    if (rc != 1) return rc;
+    if (!is_v2) {  // no instantiation for this shape: the SIMT family runs v1 unsplit
+      kp.num_parts = 1;
+      kp.partition_size = std::max(a->max_seq_len, 1);
+    }
   }
-  if (rc == 1) {
-    rc = launch_attention_simt(kp, a->num_seqs, a->dtype, a->kv_dtype, stream);
-    if (rc == B200PA_OK) g_last_attention_path = "simt";
-  }
+  rc = launch_attention_simt(kp, a->num_seqs, a->dtype, a->kv_dtype, stream);
   if (rc != B200PA_OK) return rc;
+  g_last_attention_path = "simt";
   g_last_attention_partitions = kp.num_parts;
   if (kp.num_parts > 1) return launch_attention_reduce(kp, a->num_seqs, a->dtype, stream);
   return B200PA_OK;
@@ -217,22 +236,17 @@ static int run_attention(const b200pa_attn_params_t* a, bool allow_split, cudaSt
 }  // namespace b200pa
 
 extern "C" int b200pa_paged_attention_v1(const b200pa_attn_params_t* p, b200pa_stream_t stream) {
-  return b200pa::run_attention(p, /*allow_split=*/false, stream);
+  return b200pa::run_attention(p, /*is_v2=*/false, stream);
 }
 
 extern "C" int b200pa_paged_attention_v2(const b200pa_attn_params_t* p, b200pa_stream_t stream) {
-  return b200pa::run_attention(p, /*allow_split=*/true, stream);
+  return b200pa::run_attention(p, /*is_v2=*/true, stream);
 }
 
-namespace b200pa { long long* g_sk_trace = nullptr; }
-// Developer hook: device buffer of [grid][4] int64 the persistent kernel fills with {smid, t_begin, t_end, blocks}
-// per CTA (globaltimer ns); NULL switches the trace off.
-extern "C" void b200pa_set_trace(void* device_buffer) { b200pa::g_sk_trace = static_cast<long long*>(device_buffer); }
-
-// Allocate the per-device workspace of the persistent kernel now (e.g. before a CUDA-graph capture).
+// Allocate the per-device attention workspace now (e.g. before a CUDA-graph capture).
 extern "C" int b200pa_prepare(int32_t device) {
-  b200pa::SkWorkspace ws;
-  return b200pa::sk_workspace(device, &ws);
+  b200pa::AttnWorkspace ws;
+  return b200pa::attn_workspace(device, &ws);
 }
 
 // Developer hook (tools/tune.py, tests): override one tuning knob at run time.  Keys are the
@@ -240,34 +254,19 @@ extern "C" int b200pa_prepare(int32_t device) {
 extern "C" int b200pa_set_tuning(const char* key, int32_t value) {
   if (!key) return B200PA_ERR_INVALID_ARG;
   b200pa::Tuning& t = b200pa::tuning();
-  struct { const char* k; int* v; } map[] = {
-      {"stages", &t.stages}, {"evict_normal", &t.evict_normal}, {"force_simt", &t.force_simt},
-      {"partition_size", &t.partition_size}, {"max_partition", &t.max_partition}, {"grid_ctas", &t.grid_ctas},
-      {"min_blocks_per_cta", &t.min_blocks_per_cta}, {"grid_kernel", &t.grid_kernel}, {"pool_pct", &t.pool_pct},
-      {"chunks_per_cta", &t.chunks_per_cta}, {"cs_min", &t.cs_min}};
+  struct {
+    const char* k;
+    int* v;
+  } map[] = {{"stages", &t.stages},
+             {"evict_normal", &t.evict_normal},
+             {"force_simt", &t.force_simt},
+             {"partition_size", &t.partition_size},
+             {"max_partition", &t.max_partition},
+             {"ctas_per_sm_target", &t.ctas_per_sm_target}};
   for (auto& m : map)
     if (std::strcmp(m.k, key) == 0) {
       *m.v = value;
       return B200PA_OK;
     }
   return B200PA_ERR_INVALID_ARG;
-}
-
-// Index arithmetic of the persistent kernel's work split, exported for the CPU test suite.
-extern "C" int64_t b200pa_sched_range_begin(int64_t W, int32_t G, int32_t c) { return b200pa::sk_range_begin(W, G, c); }
-extern "C" int32_t b200pa_sched_cta_of(int64_t W, int32_t G, int64_t f) { return b200pa::sk_cta_of(W, G, f); }
-extern "C" int32_t b200pa_sched_effective_ctas(int64_t W, int32_t grid) { return b200pa::sk_effective_ctas(W, grid); }
-// geometry of the chunk list: out[0..4] = {W1, Gs, cs, PC, number of chunks}
-extern "C" void b200pa_sched_geometry(int64_t W, int32_t grid, int32_t pool_pct, int32_t chunks_per_cta, int32_t cs_min,
-                                      int32_t max_chunks, int64_t* out) {
-  const b200pa::SkGeom g = b200pa::sk_geometry(W, grid, pool_pct, chunks_per_cta, cs_min, max_chunks);
-  out[0] = g.W1; out[1] = g.Gs; out[2] = g.cs; out[3] = g.PC; out[4] = b200pa::sk_num_chunks(g);
-}
-extern "C" int64_t b200pa_sched_chunk_begin(int64_t W, int32_t grid, int32_t pool_pct, int32_t chunks_per_cta,
-                                            int32_t cs_min, int32_t max_chunks, int32_t chunk) {
-  return b200pa::sk_chunk_begin(b200pa::sk_geometry(W, grid, pool_pct, chunks_per_cta, cs_min, max_chunks), chunk);
-}
-extern "C" int32_t b200pa_sched_chunk_of(int64_t W, int32_t grid, int32_t pool_pct, int32_t chunks_per_cta,
-                                         int32_t cs_min, int32_t max_chunks, int64_t f) {
-  return b200pa::sk_chunk_of(b200pa::sk_geometry(W, grid, pool_pct, chunks_per_cta, cs_min, max_chunks), f);
 }

@@ -42,17 +42,7 @@ struct AttnKernelParams {
   int bs_vert_stride;
   int bs_block_size;
   int bs_head_sliding_step;
-  // persistent (stream-K) mma kernel only
-  int num_seqs;
-  int max_seq_len;          // caller's bound; sizes the grid, never trusted for correctness
-  float* sk_slots;          // per-device workspace: 2 partial-result slots per CTA
-  unsigned* sk_counters;    // per-device workspace: one self-resetting arrival counter per CTA
-  unsigned* sk_pool;        // per-device workspace: [0] next pool chunk, [1] CTAs finished (both self-resetting)
-  int sk_max_chunks;        // workspace capacity in chunks (2 slots + 1 counter each)
-  int sk_pool_pct;          // share of the blocks handed out dynamically, percent
-  int sk_chunks_per_cta;    // pool chunks aimed at per CTA
-  int sk_cs_min;            // smallest pool chunk, blocks
-  long long* sk_trace;      // developer trace (b200pa_set_trace): [cta][4] = {smid, t_begin, t_end, blocks}, or null
+  unsigned* sk_counters;    // mma family, num_parts > 1: one self-resetting arrival counter per (sequence, KV-head unit)
 };
 
 // Tuning knobs: read from the environment ONCE, when the library is first used (never on the
@@ -61,36 +51,30 @@ struct Tuning {
   int stages = 0;           // B200PA_STAGES: TMA ring depth per warp (0 = table / deepest that fits)
   int evict_normal = -1;    // B200PA_EVICT_NORMAL: -1 = table, 0 = evict_first, 1 = evict_normal
   int force_simt = 0;       // B200PA_FORCE_SIMT: tests only — run the general SIMT family
-  int partition_size = 0;   // B200PA_PARTITION_SIZE: SIMT split size override (multiple of 512)
-  int max_partition = 4096; // B200PA_MAX_PARTITION: SIMT split size cap
-  int grid_ctas = 0;        // B200PA_GRID_CTAS: persistent kernel grid override (0 = SMs x occupancy)
-  int min_blocks_per_cta = 8;  // B200PA_MIN_BLOCKS_PER_CTA: small problems use fewer CTAs
-  int pool_pct = 25;        // B200PA_POOL_PCT: share of the KV blocks scheduled dynamically (0 = static split)
-  int chunks_per_cta = 6;   // B200PA_CHUNKS_PER_CTA: pool chunks per CTA aimed at (smaller chunks, smaller tail)
-  int cs_min = 24;          // B200PA_CS_MIN: smallest pool chunk in KV blocks
-  int grid_kernel = 0;      // B200PA_GRID_KERNEL: A/B only — the round-1 one-CTA-per-(seq, KV head, split) kernel
+  int partition_size = 0;   // B200PA_PARTITION_SIZE: split size override (multiple of 512)
+  int max_partition = 4096; // B200PA_MAX_PARTITION: split size cap
+  int ctas_per_sm_target = 8;  // B200PA_CTAS_PER_SM_TARGET: split until (sequence, KV head, split) units reach SMs x this
 };
 Tuning& tuning();
 
-// Per-device workspace of the persistent kernel (allocated once per device, on first use).
-struct SkWorkspace {
-  float* slots = nullptr;
+// Per-device workspace (allocated once per device, on first use): arrival counters of the fused
+// split-K reduce and the scratch that paged_attention_v1 splits through (its ABI carries none).
+struct AttnWorkspace {
+  char* scratch = nullptr;
+  size_t scratch_bytes = 0;
   unsigned* counters = nullptr;
-  unsigned* pool = nullptr;  // [2], right behind the counters
-  size_t slot_bytes = 0;   // bytes behind `slots`: 2 partials per CTA fit for grid <= slot_bytes / (2 * slot size)
   int max_counters = 0;
   int num_sms = 0;
 };
-constexpr size_t kSkWorkspaceSlotBytes = 48u << 20;
-constexpr int kSkMaxCounters = 16384;
-int sk_workspace(int device, SkWorkspace* ws);  // B200PA_OK or a negative status
+constexpr int kMmaMaxSplits = 64;  // most context splits per (sequence, KV head) in the mma family
+constexpr size_t kWorkspaceScratchBytes = 64u << 20;
+constexpr int kWorkspaceCounters = 1 << 20;
+int attn_workspace(int device, AttnWorkspace* ws);  // B200PA_OK or a negative status
 
 // attention_mma.cu — returns B200PA_OK, or 1 when (dtype, kv, block, head) has no MMA
 // instantiation (caller falls through to the SIMT family), or a negative status.
 int launch_attention_mma(const AttnKernelParams& kp, int num_seqs, int dtype, int kv_dtype, cudaStream_t stream);
-// persistent stream-K variant (attention_sk_kernel.cuh); *grid_out = CTAs launched
-int launch_attention_sk(const AttnKernelParams& kp, int num_seqs, int dtype, int kv_dtype, cudaStream_t stream,
-                        int* grid_out);
+
 // Shared memory the mma kernel needs for (head_size, block_size, cache bytes, stages, g-tiles).
 size_t mma_smem_bytes(int head_size, int block_size, int cache_elem_bytes, int stages, int ng);
 

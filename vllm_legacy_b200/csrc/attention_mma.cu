@@ -4,9 +4,8 @@
 
 namespace b200pa {
 
-#define B200PA_DECL(D)                                                                  \
-  int launch_attention_mma_d##D(const AttnKernelParams&, int, int, int, cudaStream_t); \
-  int launch_attention_sk_d##D(const AttnKernelParams&, int, int, int, cudaStream_t, int*);
+#define B200PA_DECL(D) \
+  int launch_attention_mma_d##D(const AttnKernelParams&, int, int, int, cudaStream_t);
 B200PA_DECL(64)
 B200PA_DECL(80)
 B200PA_DECL(96)
@@ -27,21 +26,6 @@ int launch_attention_mma(const AttnKernelParams& kp, int num_seqs, int dtype, in
     case 128: return launch_attention_mma_d128(kp, num_seqs, dtype, kv_dtype, stream);
     case 192: return launch_attention_mma_d192(kp, num_seqs, dtype, kv_dtype, stream);
     case 256: return launch_attention_mma_d256(kp, num_seqs, dtype, kv_dtype, stream);
-    default: return 1;
-  }
-}
-
-int launch_attention_sk(const AttnKernelParams& kp, int num_seqs, int dtype, int kv_dtype, cudaStream_t stream,
-                        int* grid_out) {
-  if (reinterpret_cast<uintptr_t>(kp.q) % 4 != 0 || kp.q_stride % 2 != 0) return 1;
-  switch (kp.head_size) {
-    case 64: return launch_attention_sk_d64(kp, num_seqs, dtype, kv_dtype, stream, grid_out);
-    case 80: return launch_attention_sk_d80(kp, num_seqs, dtype, kv_dtype, stream, grid_out);
-    case 96: return launch_attention_sk_d96(kp, num_seqs, dtype, kv_dtype, stream, grid_out);
-    case 112: return launch_attention_sk_d112(kp, num_seqs, dtype, kv_dtype, stream, grid_out);
-    case 128: return launch_attention_sk_d128(kp, num_seqs, dtype, kv_dtype, stream, grid_out);
-    case 192: return launch_attention_sk_d192(kp, num_seqs, dtype, kv_dtype, stream, grid_out);
-    case 256: return launch_attention_sk_d256(kp, num_seqs, dtype, kv_dtype, stream, grid_out);
     default: return 1;
   }
 }

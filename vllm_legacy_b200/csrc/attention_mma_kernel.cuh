@@ -39,6 +39,18 @@ namespace b200pa {
 
 constexpr int kMmaWarps = 4;
 constexpr int kMmaThreads = kMmaWarps * 32;
+constexpr int kMmaMaxParts = kMmaMaxSplits;  // most context splits per (sequence, KV head): the launch plan grows the split beyond
+
+// 16-/32-bit load that bypasses L1 (data written by other SMs during this launch)
+__device__ __forceinline__ float ldcg_t(const float* p) { return __ldcg(p); }
+__device__ __forceinline__ __half ldcg_t(const __half* p) {
+  const unsigned short v = __ldcg(reinterpret_cast<const unsigned short*>(p));
+  return __ushort_as_half(v);
+}
+__device__ __forceinline__ __nv_bfloat16 ldcg_t(const __nv_bfloat16* p) {
+  const unsigned short v = __ldcg(reinterpret_cast<const unsigned short*>(p));
+  return __ushort_as_bfloat16(v);
+}
 
 // ---- PTX wrappers -------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -218,7 +230,20 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
   const int NST = p.num_stages;
 
   const int t_begin = p.num_parts > 1 ? part * p.partition_size : 0;
-  if (p.num_parts > 1 && t_begin >= seq_len) return;
+  if (p.num_parts > 1 && t_begin >= seq_len) {
+    // an empty split does not take part in the merge; for an empty context split 0 writes the zeros
+    if (part == 0) {
+      const int G0 = p.num_heads / p.num_kv_heads;
+      const int HPT0 = 8 * NG;
+      const int qt0 = blockIdx.x % ((G0 + HPT0 - 1) / HPT0), kvh0 = blockIdx.x / ((G0 + HPT0 - 1) / HPT0);
+      for (int idx = threadIdx.x; idx < HPT0 * D; idx += kMmaThreads) {
+        const int hr = qt0 * HPT0 + idx / D;
+        if (hr < G0)
+          static_cast<T*>(p.out)[((int64_t)seq * p.num_heads + kvh0 * G0 + hr) * D + idx % D] = from_float<T>(0.f);
+      }
+    }
+    return;
+  }
   const int t_end = p.num_parts > 1 ? min(seq_len, t_begin + p.partition_size) : seq_len;
   const int blk_begin = t_begin / B;
   const int nblk = (t_end - t_begin + B - 1) / B;
@@ -589,6 +614,67 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
     } else {
       static_cast<T*>(p.out)[row * D + d] = from_float<T>(res);
     }
+  }
+  if (p.num_parts == 1) return;
+
+  // ---- split-K reduce, fused: the LAST split of this (sequence, KV head) to finish merges them all ------
+  // (reference: a second kernel, paged_attention_v2_reduce_kernel, attention_kernels.cu:565-669; same formula:
+  //  w_i = exp_sums_i * exp(max_i - max); out = sum_i tmp_out_i * w_i / (sum_i w_i + 1e-6)).  The arrival
+  // counter lives in the per-device workspace and is reset by the split that uses it, so every launch starts
+  // from zero; the merge order is the split order, whoever arrives last — results do not depend on timing.
+  const int n_parts = min(p.num_parts, (seq_len + p.partition_size - 1) / p.partition_size);  // non-empty splits
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  unsigned* counter = p.sk_counters + ((int64_t)seq * gridDim.x + blockIdx.x);
+  if (threadIdx.x == 0) s_last = atomicAdd(counter, 1u) == (unsigned)(n_parts - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (threadIdx.x == 0) *counter = 0u;
+  // weights per (head of this CTA, split) into shared memory: warp w takes heads w, w + 4, ...
+  float* w_s = reinterpret_cast<float*>(smem);  // [HPT][n_parts], n_parts <= kMmaMaxParts
+  for (int g = warp; g < HPT; g += kMmaWarps) {
+    const int hr = qt * HPT + g;
+    if (hr >= G) break;
+    const int64_t row = (int64_t)seq * p.num_heads + kv_head * G + hr;
+    const float* ml = p.max_logits + row * p.scratch_parts;
+    const float* es = p.exp_sums + row * p.scratch_parts;
+    float mv[kMmaMaxParts / 32], ev[kMmaMaxParts / 32], mx = -3.0e38f;
+#pragma unroll
+    for (int k = 0; k < kMmaMaxParts / 32; ++k) {
+      const int i = lane + 32 * k;
+      mv[k] = i < n_parts ? __ldcg(ml + i) : -3.0e38f;
+      ev[k] = i < n_parts ? __ldcg(es + i) : 0.f;
+      mx = fmaxf(mx, mv[k]);
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+#pragma unroll
+    for (int k = 0; k < kMmaMaxParts / 32; ++k) {
+      ev[k] *= expf(mv[k] - mx);
+      sum += ev[k];
+    }
+    sum = warp_sum(sum);
+    const float inv = __fdividef(1.f, sum + 1e-6f);
+#pragma unroll
+    for (int k = 0; k < kMmaMaxParts / 32; ++k) {
+      const int i = lane + 32 * k;
+      if (i < n_parts) w_s[g * n_parts + i] = ev[k] * inv;
+    }
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < HPT * D; idx += kMmaThreads) {
+    const int g = idx / D;
+    const int d = idx - g * D;
+    const int hr = qt * HPT + g;
+    if (hr >= G) break;
+    const int64_t row = (int64_t)seq * p.num_heads + kv_head * G + hr;
+    const T* tmp = static_cast<const T*>(p.tmp_out) + row * p.scratch_parts * D + d;
+    const float* w = w_s + g * n_parts;
+    float a = 0.f;
+    for (int i = 0; i < n_parts; ++i) a = fmaf(to_float<T>(ldcg_t(tmp + (int64_t)i * D)), w[i], a);
+    static_cast<T*>(p.out)[row * D + d] = from_float<T>(a);
   }
 }
 

@@ -503,9 +503,6 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     check_status(b200pa_read_stream_probe(src.data_ptr(), src.numel() * src.element_size(), sink.data_ptr(),
                                           current_stream()), nullptr, src, "");
   }, "Measurement aid: stream a tensor once with read-only 128-bit loads");
-  m.def("set_trace", [](const c10::optional<torch::Tensor>& buf) {
-    b200pa_set_trace(buf.has_value() ? buf->data_ptr() : nullptr);
-  }, "Developer hook: int64 CUDA tensor [grid, 4] filled with {smid, t_begin, t_end, blocks} per CTA, or None");
   m.def("prepare", [](int device) { check_status(b200pa_prepare(device), nullptr, torch::Tensor(), ""); },
         "Allocate the per-device attention workspace now (e.g. before a CUDA-graph capture)");
   m.def("set_tuning", [](const std::string& key, int value) {
