@@ -327,7 +327,7 @@ int b200pa_prepare(int32_t device);
 
 /* Developer hook (tools/tune.py, tests): override a tuning knob at run time.  The same knobs are
  * read from the environment (B200PA_<KEY>) once, when the library is first used — never per call.
- * Keys: stages, evict_normal, force_simt, partition_size, max_partition, ctas_per_sm_target. */
+ * Keys: stages, evict_normal, force_simt, partition_size, max_partition, split_cost. */
 int b200pa_set_tuning(const char* key, int32_t value);
 
 /* Measurement aid (bench.py): read `bytes` of device memory once with streaming 128-bit loads — the

@@ -2,7 +2,7 @@
 """Developer tool (GPU box): time the attention ops on the BASELINE configs under different launch knobs
 (b200pa_set_tuning keys; the library reads its environment only once, at load).  One line per (config, knob set).
 
-  python tools/tune.py --configs c2,c4 --knobs "" "stages=2" "stages=4,evict_normal=1" "ctas_per_sm_target=4"
+  python tools/tune.py --configs c2,c4 --knobs "" "stages=2" "stages=4,evict_normal=1" "split_cost=256"
 """
 import argparse
 import math
@@ -41,7 +41,7 @@ CONFIGS = {
     "short": ([200] * 1024, 32, 8, 128, 16, "auto"),       # many short sequences: item switches dominate
 }
 DEFAULTS = {"stages": 0, "evict_normal": -1, "force_simt": 0, "partition_size": 0, "max_partition": 4096,
-            "ctas_per_sm_target": 8}
+            "split_cost": 512}
 
 
 def build(name):

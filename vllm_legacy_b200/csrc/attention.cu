@@ -6,6 +6,7 @@
 //
 // Reference host side: csrc/attention/attention_kernels.cu:690-825 (v1), :844-1014 (v2).
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -27,7 +28,7 @@ Tuning& tuning() {
     v.force_simt = env_int("B200PA_FORCE_SIMT", v.force_simt);
     v.partition_size = env_int("B200PA_PARTITION_SIZE", v.partition_size);
     v.max_partition = env_int("B200PA_MAX_PARTITION", v.max_partition);
-    v.ctas_per_sm_target = std::max(1, env_int("B200PA_CTAS_PER_SM_TARGET", v.ctas_per_sm_target));
+    v.split_cost = std::max(1, env_int("B200PA_SPLIT_COST", v.split_cost));
     return v;
   }();
   return t;
@@ -176,9 +177,22 @@ static int run_attention(const b200pa_attn_params_t* a, bool is_v2, cudaStream_t
   const int64_t units = (int64_t)a->num_seqs * (mma_ok ? a->num_kv_heads * q_tiles : a->num_heads);
   const bool may_split = mma_ok ? units <= ws.max_counters : is_v2;
   if (may_split && a->max_seq_len > kRefPartition) {
-    const int64_t target = (int64_t)(mma_ok ? ws.num_sms : 148) * tn.ctas_per_sm_target;
-    const int want = (int)std::max<int64_t>(1, (target + units - 1) / units);
-    int psize = (a->max_seq_len + want - 1) / want;
+    int psize;
+    if (mma_ok) {
+      // Splits p trade the tail of the launch (the last CTAs to finish leave SMs idle for about half a CTA's
+      // duration, L / p tokens) against the fixed cost of every CTA (start-up, drain, merge: worth ~split_cost
+      // tokens of streaming), units * p / slots times: p* = sqrt(L * slots / (units * split_cost)).
+      // Measured optimum on the BASELINE shapes (profiles/r02_tune_grid_fused.log): config 2 -> 1, config 3 at
+      // TP2/4/8 -> 2/3/4, config 1 -> 1, one 32k sequence -> 32+.
+      const double slots = 2.0 * ws.num_sms;
+      const double pstar = std::sqrt((double)a->max_seq_len * slots / ((double)units * tn.split_cost));
+      const int want = std::max(1, (int)(pstar + 0.5));
+      psize = (a->max_seq_len + want - 1) / want;
+    } else {
+      const int64_t target = (int64_t)148 * 8;  // SIMT family: ~8 CTAs per SM
+      const int want = (int)std::max<int64_t>(1, (target + units - 1) / units);
+      psize = (a->max_seq_len + want - 1) / want;
+    }
     psize = std::min(psize, tn.max_partition);
     if (tn.partition_size > 0) psize = tn.partition_size;
     psize = round_up(std::max(psize, 1), kRefPartition);
@@ -262,7 +276,7 @@ extern "C" int b200pa_set_tuning(const char* key, int32_t value) {
              {"force_simt", &t.force_simt},
              {"partition_size", &t.partition_size},
              {"max_partition", &t.max_partition},
-             {"ctas_per_sm_target", &t.ctas_per_sm_target}};
+             {"split_cost", &t.split_cost}};
   for (auto& m : map)
     if (std::strcmp(m.k, key) == 0) {
       *m.v = value;

@@ -53,7 +53,7 @@ struct Tuning {
   int force_simt = 0;       // B200PA_FORCE_SIMT: tests only — run the general SIMT family
   int partition_size = 0;   // B200PA_PARTITION_SIZE: split size override (multiple of 512)
   int max_partition = 4096; // B200PA_MAX_PARTITION: split size cap
-  int ctas_per_sm_target = 8;  // B200PA_CTAS_PER_SM_TARGET: split until (sequence, KV head, split) units reach SMs x this
+  int split_cost = 512;     // B200PA_SPLIT_COST: fixed cost of one more CTA in tokens of streaming (split plan)
 };
 Tuning& tuning();
 

@@ -22,14 +22,18 @@ static int launch_one(AttnKernelParams kp, int num_seqs, cudaStream_t stream) {
   auto total_bytes = [&](int nst) { return kMmaWarps * mma_region_bytes(STAGE, nst, D, HPT) + kMmaWarps * nst * 8; };
   int nst = kp.num_stages;
   if (nst <= 0) {
-    // Deepest ring (<= 8 stages) that still lets two CTAs share an SM; if that is shallower than
-    // 3 stages take the whole SM for one CTA instead.  Bytes in flight per SM are what hide the
-    // HBM latency: 2 CTAs x 4 warps x 3 stages x 8 KiB = 192 KiB for bf16 / D128 / B16.
-    // fp8 stages are half the size: the sweep (profiles/r01_tune_sweep_attention.log) found 4 of them better
-    // than the 6 that fit — more stages only delay the first use of a landed block.
+    // Bytes in flight per SM are what hide the HBM latency (~128 KiB suffice, profiles/r02_tune_grid_fused.log);
+    // more, smaller CTAs per SM smooth over the start-up and drain bubbles of each CTA.  So: the deepest ring
+    // (>= 2 stages) that lets THREE CTAs share an SM (bf16 / D128 / B16: 3 CTAs x 4 warps x 2 stages x 8 KiB =
+    // 192 KiB), else the deepest (>= 3) that lets two, else the whole SM for one CTA.  fp8 stages are half the
+    // size: 4 of them measured better than the 6-8 that would fit (more only delay the first use of a block).
     constexpr int kMaxStages = KV == B200PA_KV_AUTO ? 8 : 4;
+    constexpr bool kThreeCtas = (D * NG <= 128);  // register file: 3 x 128 threads x <= 168 registers
     nst = 0;
-    if (kTwoCtas)
+    if (kThreeCtas)
+      for (int n = kMaxStages; n >= 2 && nst == 0; --n)
+        if (total_bytes(n) <= kSmemPerSM / 3 - kSmemReservedPerCta) nst = n;
+    if (nst == 0 && kTwoCtas)
       for (int n = kMaxStages; n >= 3 && nst == 0; --n)
         if (total_bytes(n) <= kSmemPerSM / 2 - kSmemReservedPerCta) nst = n;
     if (nst == 0)

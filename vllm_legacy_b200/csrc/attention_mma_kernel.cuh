@@ -672,9 +672,18 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
     const int64_t row = (int64_t)seq * p.num_heads + kv_head * G + hr;
     const T* tmp = static_cast<const T*>(p.tmp_out) + row * p.scratch_parts * D + d;
     const float* w = w_s + g * n_parts;
-    float a = 0.f;
-    for (int i = 0; i < n_parts; ++i) a = fmaf(to_float<T>(ldcg_t(tmp + (int64_t)i * D)), w[i], a);
-    static_cast<T*>(p.out)[row * D + d] = from_float<T>(a);
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;  // four loads in flight
+    int i = 0;
+    for (; i + 4 <= n_parts; i += 4) {
+      const T t0 = ldcg_t(tmp + (int64_t)i * D), t1 = ldcg_t(tmp + (int64_t)(i + 1) * D);
+      const T t2 = ldcg_t(tmp + (int64_t)(i + 2) * D), t3 = ldcg_t(tmp + (int64_t)(i + 3) * D);
+      a0 = fmaf(to_float<T>(t0), w[i], a0);
+      a1 = fmaf(to_float<T>(t1), w[i + 1], a1);
+      a2 = fmaf(to_float<T>(t2), w[i + 2], a2);
+      a3 = fmaf(to_float<T>(t3), w[i + 3], a3);
+    }
+    for (; i < n_parts; ++i) a0 = fmaf(to_float<T>(ldcg_t(tmp + (int64_t)i * D)), w[i], a0);
+    static_cast<T*>(p.out)[row * D + d] = from_float<T>((a0 + a1) + (a2 + a3));
   }
 }
 
