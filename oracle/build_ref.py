@@ -16,7 +16,10 @@ Both are bound through the small pybind shims in this directory
 
   prefix_prefill_ref.py          vllm/attention/ops/prefix_prefill.py staged verbatim (Triton; runs on the GPU box)
 
-Usage: python oracle/build_ref.py [cpu] [cuda] [prefill] [--force]
+  refsuite/                      the reference's tests/kernels/test_{cache,attention}.py + the Python glue they import,
+                                 staged verbatim (run over this repo's extension by tests/test_gpu_reference_suite.py)
+
+Usage: python oracle/build_ref.py [cpu] [cuda] [prefill] [suite] [--force]
 """
 import os
 import subprocess
@@ -132,6 +135,26 @@ def stage_prefix_prefill():
     print("staged", src)
 
 
+SUITE_FILES = (
+    "vllm/_custom_ops.py", "vllm/utils.py", "vllm/envs.py", "vllm/logger.py", "vllm/logging/__init__.py",
+    "vllm/logging/formatter.py", "vllm/attention/ops/paged_attn.py", "vllm/attention/ops/prefix_prefill.py",
+    "tests/kernels/test_cache.py", "tests/kernels/test_attention.py", "tests/kernels/conftest.py",
+    "tests/kernels/allclose_default.py",
+)
+
+
+def stage_reference_suite():
+    """The reference's own kernel tests and the Python glue between them and `vllm._C`, staged VERBATIM into
+    oracle/_ref/refsuite/ (git-ignored; travels to the GPU box) so that tests/test_gpu_reference_suite.py can run
+    them, unmodified, over this repo's extension mounted as `vllm._C`."""
+    import shutil
+    for rel in SUITE_FILES:
+        dst = os.path.join(OUT, "refsuite", rel)
+        os.makedirs(os.path.dirname(dst), exist_ok=True)
+        shutil.copyfile(os.path.join(REF, rel), dst)
+    print("staged", len(SUITE_FILES), "reference files into", os.path.join(OUT, "refsuite"))
+
+
 def main():
     if not os.path.isdir(CSRC):
         print(f"{REF} not present: keeping prebuilt oracle/_ref as is")
@@ -145,6 +168,8 @@ def main():
         build_cuda(force)
     if "prefill" in args or "cuda" in args:
         stage_prefix_prefill()
+    if "suite" in args or "cuda" in args:
+        stage_reference_suite()
     print(f"done in {time.time() - t0:.0f}s")
     return 0
 

@@ -216,3 +216,69 @@ def test_kv_head_sharding_world2_gloo():
         p.join(120)
         assert p.exitcode == 0
     assert q.get(timeout=10) is True
+
+
+def test_hip_backend_dense_paths(recorder, monkeypatch):
+    """The fork's own backend (hip.py:206-209, 306-319): dense layers and short contexts decode through
+    PagedAttention; everything that needs the external `hip` package raises instead of being replaced."""
+    from vllm_legacy_b200.attention.backends.hip import (HiPAttentionBackend, HiPAttentionMetadata,
+                                                        HiPSparsePathUnavailable)
+    Hq, Hkv, D, B, nb, S = 8, 2, 64, 16, 4, 3
+    assert HiPAttentionBackend.get_kv_cache_shape(nb, B, Hkv, D) == (2, nb, B * Hkv * D)
+    with pytest.raises(AssertionError):  # layer_index is mandatory in the fork (hip.py:103)
+        HiPAttentionBackend.get_impl_cls()(Hq, D, 0.125, Hkv, None, None, "auto")
+
+    def meta(max_len):
+        return HiPAttentionBackend.make_metadata(
+            seq_lens_tensor=torch.tensor([3, 5, 9], dtype=torch.int32), max_decode_seq_len=max_len,
+            block_tables=torch.zeros(S, 1, dtype=torch.int32), num_prefills=0, num_prefill_tokens=0,
+            num_decode_tokens=S, slot_mapping=torch.tensor([2, 4, 8]))
+    assert isinstance(meta(9), HiPAttentionMetadata)
+    kv_cache = torch.zeros(*HiPAttentionBackend.get_kv_cache_shape(nb, B, Hkv, D))
+    args = (torch.zeros(S, Hq * D), torch.zeros(S, Hkv * D), torch.zeros(S, Hkv * D), kv_cache)
+    # a dense layer (index < HIP_DENSE_LAYERS = 3): any context length
+    dense = HiPAttentionBackend.get_impl_cls()(Hq, D, 0.125, Hkv, None, None, "auto", None, layer_index=1)
+    assert dense.forward(*args, meta(100000)).shape == (S, Hq * D)
+    assert [c[0] for c in recorder.calls] == ["reshape_and_cache", "paged_attention_v2"]
+    # a sparse layer: PagedAttention while max_decode_seq_len < 3 * HIP_K, the external package beyond
+    recorder.calls.clear()
+    sparse = HiPAttentionBackend.get_impl_cls()(Hq, D, 0.125, Hkv, None, None, "auto", None, layer_index=7)
+    assert sparse.forward(*args, meta(3 * 1024 - 1)).shape == (S, Hq * D)
+    assert [c[0] for c in recorder.calls] == ["reshape_and_cache", "paged_attention_v2"]
+    with pytest.raises(HiPSparsePathUnavailable):
+        sparse.forward(*args, meta(3 * 1024))
+    monkeypatch.setenv("HIP_K", "64")
+    assert HiPAttentionBackend.get_impl_cls()(Hq, D, 0.125, Hkv, None, None, "auto", None, layer_index=7).hip_k == 64
+    with pytest.raises(AssertionError):
+        dense.forward(*args, meta(9), 0.5)  # kv_scale != 1 is rejected by the fork (hip.py:143)
+
+
+def test_selector(monkeypatch):
+    """vllm/attention/selector.py:24-167: env override, the fork's HIP_ATTN entry, the reference's FLASH_ATTN exclusions."""
+    from vllm_legacy_b200.attention import selector
+    from vllm_legacy_b200.attention.backends.hip import HiPAttentionBackend
+    assert [m.name for m in selector._Backend] == ["FLASH_ATTN", "XFORMERS", "ROCM_FLASH", "TORCH_SDPA", "FLASHINFER",
+                                                   "HIP_ATTN"]
+    a = (32, 128, 8, None, torch.bfloat16, "auto", 16)
+    monkeypatch.delenv("VLLM_ATTENTION_BACKEND", raising=False)
+    assert selector.which_attn_to_use(*a) == selector._Backend.FLASH_ATTN
+    assert selector.which_attn_to_use(32, 128, 8, None, torch.bfloat16, "fp8", 16) == selector._Backend.XFORMERS
+    assert selector.which_attn_to_use(32, 128, 8, None, torch.float32, "auto", 16) == selector._Backend.XFORMERS
+    assert selector.which_attn_to_use(32, 128, 8, 4096, torch.bfloat16, "auto", 16) == selector._Backend.XFORMERS
+    assert selector.which_attn_to_use(32, 128, 8, None, torch.bfloat16, "auto", 8) == selector._Backend.XFORMERS
+    assert selector.which_attn_to_use(32, 80, 8, None, torch.bfloat16, "auto", 16) == selector._Backend.XFORMERS
+    monkeypatch.setenv("VLLM_ATTENTION_BACKEND", "HIP_ATTN")
+    selector.get_attn_backend.cache_clear()
+    assert selector.get_attn_backend(*a) is HiPAttentionBackend
+    monkeypatch.setenv("VLLM_ATTENTION_BACKEND", "XFORMERS")
+    selector.get_attn_backend.cache_clear()
+    assert selector.get_attn_backend(*a) is B200PagedAttentionBackend
+    assert selector.get_attn_backend(*a, is_blocksparse=True) is B200PagedAttentionBackend
+    monkeypatch.setenv("VLLM_ATTENTION_BACKEND", "ROCM_FLASH")
+    selector.get_attn_backend.cache_clear()
+    with pytest.raises(ValueError, match="sm_100a"):
+        selector.get_attn_backend(*a)
+    monkeypatch.setenv("VLLM_ATTENTION_BACKEND", "NOPE")
+    with pytest.raises(ValueError, match="Invalid attention backend"):
+        selector.which_attn_to_use(*a)
+    selector.get_attn_backend.cache_clear()

@@ -191,10 +191,9 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
         """Prompt run (xformers.py:291-318).  With a cached prefix the reference calls
         PagedAttention.forward_prefix; without one (no cache yet, or empty block tables) it runs plain causal
         attention through xformers — here that is the same kernel with every context length 0."""
-        assert self.kv_cache_dtype == "auto", \
-            "prefix-prefill over an fp8 KV cache is unsupported (as in the reference, xformers.py:301-304)"
         no_prefix = key_cache is None or meta.block_tables is None or meta.block_tables.numel() == 0
         if no_prefix:
+            # plain causal attention over the new tokens only: the (possibly fp8) cache is not read (xformers.py:291-300)
             dev, nseq = query.device, meta.num_prefills
             key_cache = torch.empty(1, self.num_kv_heads, self.head_size // 8, 8, 8, dtype=query.dtype, device=dev)
             value_cache = torch.empty(1, self.num_kv_heads, self.head_size, 8, dtype=query.dtype, device=dev)
