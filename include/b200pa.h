@@ -112,6 +112,19 @@ int b200pa_paged_attention_v1(const b200pa_attn_params_t* p, b200pa_stream_t str
 int b200pa_paged_attention_v2(const b200pa_attn_params_t* p, b200pa_stream_t stream);
 
 /*
+ * paged_attention_flash — decode over the flash-attention cache layout
+ * replaces: flash_attn_with_kvcache(q.unsqueeze(1), key_cache, value_cache, block_table=..., cache_seqlens=...,
+ *           softmax_scale=..., causal=True, alibi_slopes=...) as called for decode by the FLASH_ATTN backend
+ *           (vllm/attention/backends/flash_attn.py:354-367); the cache is written by reshape_and_cache_flash.
+ *   key_cache, value_cache  [num_blocks, block_size, num_kv_heads, head_size] dtype (f16 | bf16), with
+ *                           kv_block_stride = stride(0), kv_token_stride = stride(1), kv_head_stride = stride(2)
+ *                           in elements, head_size contiguous, rows 16-byte aligned
+ *   head_size in {32, 64, ..., 256} (multiples of 32), block_size 16 | 32, kv_dtype AUTO, no block-sparse.
+ * Everything else as paged_attention_v1 (no caller scratch: long contexts split through the per-device workspace).
+ */
+int b200pa_paged_attention_flash(const b200pa_attn_params_t* p, int64_t kv_token_stride, b200pa_stream_t stream);
+
+/*
  * reshape_and_cache
  * replaces: csrc/cache.h:15-25, csrc/cache_kernels.cu:150-202, 241-287.
  *   key, value   [num_tokens, num_heads, head_size] dtype, row strides key_stride/value_stride

@@ -282,3 +282,21 @@ def test_selector(monkeypatch):
     with pytest.raises(ValueError, match="Invalid attention backend"):
         selector.which_attn_to_use(*a)
     selector.get_attn_backend.cache_clear()
+
+
+def test_flash_backend_interface(monkeypatch):
+    """flash_attn.py:18-67: cache shape, block-size rule, head sizes; the selector hands it out for FLASH_ATTN."""
+    from vllm_legacy_b200.attention import selector
+    from vllm_legacy_b200.attention.backends.b200_flash import B200FlashAttentionBackend as FB
+    assert FB.get_kv_cache_shape(7, 16, 8, 128) == (2, 7, 16, 8, 128)
+    with pytest.raises(ValueError, match="multiple of 16"):
+        FB.get_kv_cache_shape(7, 8, 8, 128)
+    assert FB.get_supported_head_sizes() == [32, 64, 96, 128, 160, 192, 224, 256]
+    with pytest.raises(ValueError, match="Head size 80"):
+        FB.get_impl_cls()(8, 80, 1.0, 2, None, None, "auto")
+    with pytest.raises(ValueError, match="Sliding window"):
+        FB.get_impl_cls()(8, 64, 1.0, 2, None, 128, "auto")
+    monkeypatch.delenv("VLLM_ATTENTION_BACKEND", raising=False)
+    selector.get_attn_backend.cache_clear()
+    assert selector.get_attn_backend(32, 128, 8, None, torch.bfloat16, "auto", 16) is FB
+    selector.get_attn_backend.cache_clear()

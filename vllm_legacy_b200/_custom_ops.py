@@ -79,6 +79,16 @@ def paged_attention_v2(
         blocksparse_block_size, blocksparse_head_sliding_step)
 
 
+def paged_attention_flash(out: torch.Tensor, query: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                          scale: float, block_tables: torch.Tensor, seq_lens: torch.Tensor, max_seq_len: int,
+                          alibi_slopes: Optional[torch.Tensor] = None) -> None:
+    """Decode attention over the flash-attention cache layout `[num_blocks, block_size, num_kv_heads, head_size]`
+    (the FLASH_ATTN / FLASHINFER backends' layout; the reference decodes it with the external
+    flash_attn_with_kvcache, vllm/attention/backends/flash_attn.py:354-367).  Not in the reference's op list."""
+    vllm_ops.paged_attention_flash(out, query, key_cache, value_cache, scale, block_tables, seq_lens, max_seq_len,
+                                   alibi_slopes)
+
+
 # pos encoding ops (vllm/_custom_ops.py:103-124); in place on query and key
 def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor, head_size: int,
                      cos_sin_cache: torch.Tensor, is_neox: bool) -> None:

@@ -96,13 +96,25 @@ constexpr int kRefPartition = 512;  // granularity the callers size the v2 scrat
 
 static int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
-static int run_attention(const b200pa_attn_params_t* a, bool is_v2, cudaStream_t stream) {
+// layout: 0 = the reference's paged layout (K [nb,H,D/x,B,x], V [nb,H,D,B]); 1 = flash layout (K, V [nb,B,H,D])
+static int run_attention(const b200pa_attn_params_t* a, bool is_v2, cudaStream_t stream, int layout = 0,
+                         int64_t kv_token_stride = 0) {
   if (!a) return B200PA_ERR_INVALID_ARG;
   if (a->kv_dtype != B200PA_KV_AUTO && a->kv_dtype != B200PA_KV_FP8_E4M3 && a->kv_dtype != B200PA_KV_FP8_E5M2)
     return B200PA_ERR_KV_DTYPE;
   if (a->dtype != B200PA_F16 && a->dtype != B200PA_BF16 && a->dtype != B200PA_F32) return B200PA_ERR_INPUT_DTYPE;
-  if (!block_size_supported(a->block_size)) return B200PA_ERR_BLOCK_SIZE;
-  if (!head_size_supported(a->head_size)) return B200PA_ERR_HEAD_SIZE;
+  if (layout == 1) {  // flash_attn.py:24-25, :37-44 (block size a multiple of 16, 16-bit only, no fp8)
+    if (a->block_size != 16 && a->block_size != 32) return B200PA_ERR_BLOCK_SIZE;
+    if (!flash_head_size_supported(a->head_size)) return B200PA_ERR_HEAD_SIZE;
+    if (a->kv_dtype != B200PA_KV_AUTO) return B200PA_ERR_KV_DTYPE;
+    if (a->dtype == B200PA_F32) return B200PA_ERR_INPUT_DTYPE;
+    if (a->blocksparse_vert_stride > 1 || reinterpret_cast<uintptr_t>(a->query) % 4 != 0 || a->q_stride % 2 != 0 ||
+        (kv_token_stride * 2) % 16 != 0)
+      return B200PA_ERR_INVALID_ARG;
+  } else {
+    if (!block_size_supported(a->block_size)) return B200PA_ERR_BLOCK_SIZE;
+    if (!head_size_supported(a->head_size)) return B200PA_ERR_HEAD_SIZE;
+  }
   if (a->num_seqs < 0 || a->num_heads <= 0 || a->num_kv_heads <= 0 || a->num_heads % a->num_kv_heads != 0 ||
       a->max_seq_len < 0 || a->max_num_blocks_per_seq < 0)
     return B200PA_ERR_INVALID_ARG;
@@ -130,6 +142,7 @@ static int run_attention(const b200pa_attn_params_t* a, bool is_v2, cudaStream_t
   kp.q_stride = a->q_stride;
   kp.kv_block_stride = a->kv_block_stride;
   kp.kv_head_stride = a->kv_head_stride;
+  kp.kv_token_stride = kv_token_stride;
   kp.num_heads = a->num_heads;
   kp.num_kv_heads = a->num_kv_heads;
   kp.head_size = a->head_size;
@@ -150,8 +163,9 @@ static int run_attention(const b200pa_attn_params_t* a, bool is_v2, cudaStream_t
   if (blocksparse && (a->blocksparse_block_size <= 0 || a->blocksparse_block_size % a->block_size != 0))
     return B200PA_ERR_INVALID_ARG;
   // TMA + mma.sync family: 16-bit queries, block size 16 / 32, dense, 4-byte aligned query rows
-  const bool mma_ok = !blocksparse && a->dtype != B200PA_F32 && a->block_size != 8 && tn.force_simt == 0 &&
-                      reinterpret_cast<uintptr_t>(a->query) % 4 == 0 && a->q_stride % 2 == 0;
+  const bool mma_ok = layout == 1 ||
+                      (!blocksparse && a->dtype != B200PA_F32 && a->block_size != 8 && tn.force_simt == 0 &&
+                       reinterpret_cast<uintptr_t>(a->query) % 4 == 0 && a->q_stride % 2 == 0);
 
   // ---- split plan -----------------------------------------------------------------------
   // One CTA streams the KV of one (sequence, KV head[, split]) for the whole GQA group (mma family)
@@ -227,9 +241,11 @@ static int run_attention(const b200pa_attn_params_t* a, bool is_v2, cudaStream_t
 
   int rc = 1;
   if (mma_ok) {
-    rc = launch_attention_mma(kp, a->num_seqs, a->dtype, a->kv_dtype, stream);
+    rc = layout == 1 ? launch_attention_flash(kp, a->num_seqs, a->dtype, stream)
+                     : launch_attention_mma(kp, a->num_seqs, a->dtype, a->kv_dtype, stream);
+    if (layout == 1 && rc == 1) return B200PA_ERR_HEAD_SIZE;  // (no other family reads this layout)
     if (rc == B200PA_OK) {
-      g_last_attention_path = "mma_tma";
+      g_last_attention_path = layout == 1 ? "mma_flash" : "mma_tma";
       g_last_attention_partitions = kp.num_parts;
       return B200PA_OK;  // (the reduce is part of the kernel)
     }
@@ -255,6 +271,11 @@ extern "C" int b200pa_paged_attention_v1(const b200pa_attn_params_t* p, b200pa_s
 
 extern "C" int b200pa_paged_attention_v2(const b200pa_attn_params_t* p, b200pa_stream_t stream) {
   return b200pa::run_attention(p, /*is_v2=*/true, stream);
+}
+
+extern "C" int b200pa_paged_attention_flash(const b200pa_attn_params_t* p, int64_t kv_token_stride,
+                                            b200pa_stream_t stream) {
+  return b200pa::run_attention(p, /*is_v2=*/false, stream, /*layout=*/1, kv_token_stride);
 }
 
 // Allocate the per-device attention workspace now (e.g. before a CUDA-graph capture).

@@ -25,6 +25,7 @@ struct AttnKernelParams {
   int64_t q_stride;
   int64_t kv_block_stride;  // elements
   int64_t kv_head_stride;   // elements
+  int64_t kv_token_stride;  // elements; flash layout [nb, B, H, D] only
   int num_heads;
   int num_kv_heads;
   int head_size;
@@ -81,6 +82,11 @@ size_t mma_smem_bytes(int head_size, int block_size, int cache_elem_bytes, int s
 // attention_simt.cu
 int launch_attention_simt(const AttnKernelParams& kp, int num_seqs, int dtype, int kv_dtype, cudaStream_t stream);
 int launch_attention_reduce(const AttnKernelParams& kp, int num_seqs, int dtype, cudaStream_t stream);
+
+// attention_flash.cu — decode over the flash-attention cache layout [num_blocks, block_size, num_kv_heads, head_size];
+// returns B200PA_OK, 1 when (dtype, head size, block size) has no instantiation, or a negative status.
+int launch_attention_flash(const AttnKernelParams& kp, int num_seqs, int dtype, cudaStream_t stream);
+bool flash_head_size_supported(int d);
 
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll

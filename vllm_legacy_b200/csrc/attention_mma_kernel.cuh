@@ -192,6 +192,122 @@ __host__ __device__ constexpr int mma_region_bytes(int stage_bytes, int stages, 
   return (m + 127) / 128 * 128;
 }
 
+// ---- shared epilogue of the tensor-core decode kernels (paged layout and flash layout) ---------------------
+// On entry every warp has left its partial state for the CTA's HPT query heads in its own shared-memory region
+// (floats): [0,16) running maxima (log2 domain), [16,32) sums, then O as [HPT][D + 4].  Merges the four warps,
+// writes the output row (one split) or the split's partial in the reference's v2 scratch format — and, for split
+// launches, lets the LAST split of this (sequence, KV head) to finish do the split-K reduce.
+template <typename T, int D, int HPT>
+__device__ __forceinline__ void decode_epilogue(const AttnKernelParams& p, uint8_t* smem, int region, int seq,
+                                                int seq_len, int kv_head, int qt, int G, int part, float out_scale) {
+  constexpr int OROW = D + 4;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  __syncthreads();
+
+  for (int idx = threadIdx.x; idx < HPT * D; idx += kMmaThreads) {
+    const int g = idx / D;
+    const int d = idx - g * D;
+    const int hr = qt * HPT + g;
+    if (hr >= G) break;  // g is non-decreasing in idx
+    float mw[kMmaWarps], m_all = kNegBig;
+#pragma unroll
+    for (int w = 0; w < kMmaWarps; ++w) {
+      mw[w] = reinterpret_cast<const float*>(smem + w * region)[g];
+      m_all = fmaxf(m_all, mw[w]);
+    }
+    float l_all = 0.f, o = 0.f;
+#pragma unroll
+    for (int w = 0; w < kMmaWarps; ++w) {
+      const float* mow = reinterpret_cast<const float*>(smem + w * region);
+      const float f = exp2f(mw[w] - m_all);
+      l_all = fmaf(mow[16 + g], f, l_all);
+      o = fmaf(mow[32 + g * OROW + d], f, o);
+    }
+    const float res = o * out_scale * __fdividef(1.f, l_all + 1e-6f);
+    const int64_t row = (int64_t)seq * p.num_heads + kv_head * G + hr;
+    if (p.num_parts > 1) {
+      static_cast<T*>(p.tmp_out)[(row * p.scratch_parts + part) * D + d] = from_float<T>(res);
+      if (d == 0) {
+        p.max_logits[row * p.scratch_parts + part] = m_all * kLn2;
+        p.exp_sums[row * p.scratch_parts + part] = l_all;
+      }
+    } else {
+      static_cast<T*>(p.out)[row * D + d] = from_float<T>(res);
+    }
+  }
+  if (p.num_parts == 1) return;
+
+  // ---- split-K reduce, fused: the LAST split of this (sequence, KV head) to finish merges them all ------
+  // (reference: a second kernel, paged_attention_v2_reduce_kernel, attention_kernels.cu:565-669; same formula:
+  //  w_i = exp_sums_i * exp(max_i - max); out = sum_i tmp_out_i * w_i / (sum_i w_i + 1e-6)).  The arrival
+  // counter lives in the per-device workspace and is reset by the split that uses it, so every launch starts
+  // from zero; the merge order is the split order, whoever arrives last — results do not depend on timing.
+  const int n_parts = min(p.num_parts, (seq_len + p.partition_size - 1) / p.partition_size);  // non-empty splits
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  unsigned* counter = p.sk_counters + ((int64_t)seq * gridDim.x + blockIdx.x);
+  if (threadIdx.x == 0) s_last = atomicAdd(counter, 1u) == (unsigned)(n_parts - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (threadIdx.x == 0) *counter = 0u;
+  // weights per (head of this CTA, split) into shared memory: warp w takes heads w, w + 4, ...
+  float* w_s = reinterpret_cast<float*>(smem);  // [HPT][n_parts], n_parts <= kMmaMaxParts
+  for (int g = warp; g < HPT; g += kMmaWarps) {
+    const int hr = qt * HPT + g;
+    if (hr >= G) break;
+    const int64_t row = (int64_t)seq * p.num_heads + kv_head * G + hr;
+    const float* ml = p.max_logits + row * p.scratch_parts;
+    const float* es = p.exp_sums + row * p.scratch_parts;
+    float mv[kMmaMaxParts / 32], ev[kMmaMaxParts / 32], mx = -3.0e38f;
+#pragma unroll
+    for (int k = 0; k < kMmaMaxParts / 32; ++k) {
+      const int i = lane + 32 * k;
+      mv[k] = i < n_parts ? __ldcg(ml + i) : -3.0e38f;
+      ev[k] = i < n_parts ? __ldcg(es + i) : 0.f;
+      mx = fmaxf(mx, mv[k]);
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+#pragma unroll
+    for (int k = 0; k < kMmaMaxParts / 32; ++k) {
+      ev[k] *= expf(mv[k] - mx);
+      sum += ev[k];
+    }
+    sum = warp_sum(sum);
+    const float inv = __fdividef(1.f, sum + 1e-6f);
+#pragma unroll
+    for (int k = 0; k < kMmaMaxParts / 32; ++k) {
+      const int i = lane + 32 * k;
+      if (i < n_parts) w_s[g * n_parts + i] = ev[k] * inv;
+    }
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < HPT * D; idx += kMmaThreads) {
+    const int g = idx / D;
+    const int d = idx - g * D;
+    const int hr = qt * HPT + g;
+    if (hr >= G) break;
+    const int64_t row = (int64_t)seq * p.num_heads + kv_head * G + hr;
+    const T* tmp = static_cast<const T*>(p.tmp_out) + row * p.scratch_parts * D + d;
+    const float* w = w_s + g * n_parts;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;  // four loads in flight
+    int i = 0;
+    for (; i + 4 <= n_parts; i += 4) {
+      const T t0 = ldcg_t(tmp + (int64_t)i * D), t1 = ldcg_t(tmp + (int64_t)(i + 1) * D);
+      const T t2 = ldcg_t(tmp + (int64_t)(i + 2) * D), t3 = ldcg_t(tmp + (int64_t)(i + 3) * D);
+      a0 = fmaf(to_float<T>(t0), w[i], a0);
+      a1 = fmaf(to_float<T>(t1), w[i + 1], a1);
+      a2 = fmaf(to_float<T>(t2), w[i + 2], a2);
+      a3 = fmaf(to_float<T>(t3), w[i + 3], a3);
+    }
+    for (; i < n_parts; ++i) a0 = fmaf(to_float<T>(ldcg_t(tmp + (int64_t)i * D)), w[i], a0);
+    static_cast<T*>(p.out)[row * D + d] = from_float<T>((a0 + a1) + (a2 + a3));
+  }
+}
+
 // T: query/out type (half | bf16).  KV: b200pa_kv_dtype_t.  D: head size.  B: block size (16|32).
 // NG: 8-row query-head tiles per CTA (1: group <= 8, 2: group <= 16 per CTA).
 template <typename T, int KV, int D, int B, int NG>
@@ -581,110 +697,7 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
       o0[OROW + 8] = oacc[r][dt][3];
     }
   }
-  __syncthreads();
-
-  const float out_scale = FP8 ? p.kv_scale : 1.f;
-  for (int idx = threadIdx.x; idx < HPT * D; idx += kMmaThreads) {
-    const int g = idx / D;
-    const int d = idx - g * D;
-    const int hr = qt * HPT + g;
-    if (hr >= G) break;  // g is non-decreasing in idx
-    float mw[kMmaWarps], m_all = kNegBig;
-#pragma unroll
-    for (int w = 0; w < kMmaWarps; ++w) {
-      mw[w] = reinterpret_cast<const float*>(smem + w * region)[g];
-      m_all = fmaxf(m_all, mw[w]);
-    }
-    float l_all = 0.f, o = 0.f;
-#pragma unroll
-    for (int w = 0; w < kMmaWarps; ++w) {
-      const float* mow = reinterpret_cast<const float*>(smem + w * region);
-      const float f = exp2f(mw[w] - m_all);
-      l_all = fmaf(mow[16 + g], f, l_all);
-      o = fmaf(mow[32 + g * OROW + d], f, o);
-    }
-    const float res = o * out_scale * __fdividef(1.f, l_all + 1e-6f);
-    const int64_t row = (int64_t)seq * p.num_heads + kv_head * G + hr;
-    if (p.num_parts > 1) {
-      static_cast<T*>(p.tmp_out)[(row * p.scratch_parts + part) * D + d] = from_float<T>(res);
-      if (d == 0) {
-        p.max_logits[row * p.scratch_parts + part] = m_all * kLn2;
-        p.exp_sums[row * p.scratch_parts + part] = l_all;
-      }
-    } else {
-      static_cast<T*>(p.out)[row * D + d] = from_float<T>(res);
-    }
-  }
-  if (p.num_parts == 1) return;
-
-  // ---- split-K reduce, fused: the LAST split of this (sequence, KV head) to finish merges them all ------
-  // (reference: a second kernel, paged_attention_v2_reduce_kernel, attention_kernels.cu:565-669; same formula:
-  //  w_i = exp_sums_i * exp(max_i - max); out = sum_i tmp_out_i * w_i / (sum_i w_i + 1e-6)).  The arrival
-  // counter lives in the per-device workspace and is reset by the split that uses it, so every launch starts
-  // from zero; the merge order is the split order, whoever arrives last — results do not depend on timing.
-  const int n_parts = min(p.num_parts, (seq_len + p.partition_size - 1) / p.partition_size);  // non-empty splits
-  __shared__ int s_last;
-  __threadfence();
-  __syncthreads();
-  unsigned* counter = p.sk_counters + ((int64_t)seq * gridDim.x + blockIdx.x);
-  if (threadIdx.x == 0) s_last = atomicAdd(counter, 1u) == (unsigned)(n_parts - 1);
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  if (threadIdx.x == 0) *counter = 0u;
-  // weights per (head of this CTA, split) into shared memory: warp w takes heads w, w + 4, ...
-  float* w_s = reinterpret_cast<float*>(smem);  // [HPT][n_parts], n_parts <= kMmaMaxParts
-  for (int g = warp; g < HPT; g += kMmaWarps) {
-    const int hr = qt * HPT + g;
-    if (hr >= G) break;
-    const int64_t row = (int64_t)seq * p.num_heads + kv_head * G + hr;
-    const float* ml = p.max_logits + row * p.scratch_parts;
-    const float* es = p.exp_sums + row * p.scratch_parts;
-    float mv[kMmaMaxParts / 32], ev[kMmaMaxParts / 32], mx = -3.0e38f;
-#pragma unroll
-    for (int k = 0; k < kMmaMaxParts / 32; ++k) {
-      const int i = lane + 32 * k;
-      mv[k] = i < n_parts ? __ldcg(ml + i) : -3.0e38f;
-      ev[k] = i < n_parts ? __ldcg(es + i) : 0.f;
-      mx = fmaxf(mx, mv[k]);
-    }
-    mx = warp_max(mx);
-    float sum = 0.f;
-#pragma unroll
-    for (int k = 0; k < kMmaMaxParts / 32; ++k) {
-      ev[k] *= expf(mv[k] - mx);
-      sum += ev[k];
-    }
-    sum = warp_sum(sum);
-    const float inv = __fdividef(1.f, sum + 1e-6f);
-#pragma unroll
-    for (int k = 0; k < kMmaMaxParts / 32; ++k) {
-      const int i = lane + 32 * k;
-      if (i < n_parts) w_s[g * n_parts + i] = ev[k] * inv;
-    }
-  }
-  __syncthreads();
-  for (int idx = threadIdx.x; idx < HPT * D; idx += kMmaThreads) {
-    const int g = idx / D;
-    const int d = idx - g * D;
-    const int hr = qt * HPT + g;
-    if (hr >= G) break;
-    const int64_t row = (int64_t)seq * p.num_heads + kv_head * G + hr;
-    const T* tmp = static_cast<const T*>(p.tmp_out) + row * p.scratch_parts * D + d;
-    const float* w = w_s + g * n_parts;
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;  // four loads in flight
-    int i = 0;
-    for (; i + 4 <= n_parts; i += 4) {
-      const T t0 = ldcg_t(tmp + (int64_t)i * D), t1 = ldcg_t(tmp + (int64_t)(i + 1) * D);
-      const T t2 = ldcg_t(tmp + (int64_t)(i + 2) * D), t3 = ldcg_t(tmp + (int64_t)(i + 3) * D);
-      a0 = fmaf(to_float<T>(t0), w[i], a0);
-      a1 = fmaf(to_float<T>(t1), w[i + 1], a1);
-      a2 = fmaf(to_float<T>(t2), w[i + 2], a2);
-      a3 = fmaf(to_float<T>(t3), w[i + 3], a3);
-    }
-    for (; i < n_parts; ++i) a0 = fmaf(to_float<T>(ldcg_t(tmp + (int64_t)i * D)), w[i], a0);
-    static_cast<T*>(p.out)[row * D + d] = from_float<T>((a0 + a1) + (a2 + a3));
-  }
+  decode_epilogue<T, D, HPT>(p, smem, region, seq, seq_len, kv_head, qt, G, part, FP8 ? p.kv_scale : 1.f);
 }
 
 }  // namespace b200pa

@@ -79,24 +79,29 @@ __global__ void reshape_and_cache_vec_kernel(const T* __restrict__ key, const T*
   CT* kblk = key_cache + block_idx * (int64_t)num_heads * head_size * block_size;
   CT* vblk = value_cache + block_idx * (int64_t)num_heads * head_size * block_size;
 
-  for (int g = threadIdx.x; g < n_groups; g += blockDim.x) {
+  // 2 * n_groups work items: the K groups, then the V groups (a decode step is latency-bound: more threads
+  // per token, each with one load and its stores, finish sooner than fewer threads doing K and V in turn)
+  for (int w = threadIdx.x; w < 2 * n_groups; w += blockDim.x) {
+    const bool is_v = w >= n_groups;
+    const int g = is_v ? w - n_groups : w;
     const int h = g / groups_per_head;
     const int dx = g % groups_per_head;
     const int e0 = h * head_size + dx * X;  // first source element of the group
-    union { int4 v[SRC_VECS]; T e[X]; } kin, vin;
+    union { int4 v[SRC_VECS]; T e[X]; } in;
+    const T* src = (is_v ? vsrc : ksrc) + e0;
 #pragma unroll
-    for (int j = 0; j < SRC_VECS; ++j) {
-      kin.v[j] = ld_nc_v4(ksrc + e0 + j * EPV);
-      vin.v[j] = ld_nc_v4(vsrc + e0 + j * EPV);
+    for (int j = 0; j < SRC_VECS; ++j) in.v[j] = ld_nc_v4(src + j * EPV);
+    if (!is_v) {
+      union { int4 v; CT e[X]; } kout;
+#pragma unroll
+      for (int j = 0; j < X; ++j) kout.e[j] = CacheStore<T, KV>::cvt(in.e[j], kv_scale);
+      CT* kdst = kblk + ((int64_t)(h * groups_per_head + dx) * block_size + block_off) * X;
+      *reinterpret_cast<int4*>(kdst) = kout.v;
+    } else {
+      CT* vdst = vblk + ((int64_t)h * head_size + dx * X) * block_size + block_off;
+#pragma unroll
+      for (int j = 0; j < X; ++j) vdst[(int64_t)j * block_size] = CacheStore<T, KV>::cvt(in.e[j], kv_scale);
     }
-    union { int4 v; CT e[X]; } kout;
-#pragma unroll
-    for (int j = 0; j < X; ++j) kout.e[j] = CacheStore<T, KV>::cvt(kin.e[j], kv_scale);
-    CT* kdst = kblk + ((int64_t)(h * groups_per_head + dx) * block_size + block_off) * X;
-    *reinterpret_cast<int4*>(kdst) = kout.v;
-    CT* vdst = vblk + ((int64_t)h * head_size + dx * X) * block_size + block_off;
-#pragma unroll
-    for (int j = 0; j < X; ++j) vdst[(int64_t)j * block_size] = CacheStore<T, KV>::cvt(vin.e[j], kv_scale);
   }
 }
 
@@ -170,30 +175,55 @@ __global__ void __launch_bounds__(kTileThreads)
   }
   __syncthreads();
 
-  // ---- write out: thread = (token j = tid % TT, row lane = tid / TT); token fastest across lanes -------
+  // ---- write out ---------------------------------------------------------------------------------------------
   // dst(K) = kc + b*H*D*B + ((h*G + dx)*B + o)*X with h*G + dx = h0*G + u   (G = D/X groups per head)
   // dst(V) = vc + b*H*D*B + (h*D + d)*B + o      with h*D + d  = h0*D + e
-  // so each thread needs its token's (b, o) once and then walks u / e with a constant stride.
-  const int j = threadIdx.x % TT;
-  const int r0 = threadIdx.x / TT;
-  constexpr int RL = kTileThreads / TT;  // row lanes
-  const int64_t slot = slot_s[j];
-  if (slot < 0) return;
-  const int64_t b = slot / block_size;
-  const int o = (int)(slot - b * block_size);
   const int64_t blk_elems = (int64_t)num_heads * head_size * block_size;
   const int groups_per_head = head_size / X;
-  CT* kdst = key_cache + b * blk_elems + ((int64_t)h0 * groups_per_head * block_size + o) * X;
-  CT* vdst = value_cache + b * blk_elems + (int64_t)h0 * head_size * block_size + o;
-  const CT* ksrc = ks + j * rsk;
-  const CT* vsrc = vs + j * rsv;
   const int n_groups = n / X;
   const int64_t kstep = (int64_t)block_size * X;
+  // Is the tile one run of consecutive slots (a prompt filling its blocks in order)?  Then the TOKEN index goes
+  // fastest across lanes: a warp's K stores cover 512 contiguous bytes and its V stores fill whole 32-byte
+  // sectors.  Scattered slots (a decode batch, a shuffled mapping) gain nothing from that order — every token
+  // lands in another block — so they are written token by token with the row index fastest, which keeps the 256
+  // threads on one token's rows (the reference's order, cache_kernels.cu:169-200) and is what the L2 merges best.
+  bool run = true;
+#pragma unroll
+  for (int t = 1; t < TT; ++t) run &= (slot_s[t] == slot_s[0] + t);
+  run &= slot_s[0] >= 0;
+  if (run) {
+    // thread = (token j = tid % TT, row lane = tid / TT)
+    const int j = threadIdx.x % TT;
+    const int r0 = threadIdx.x / TT;
+    constexpr int RL = kTileThreads / TT;  // row lanes
+    const int64_t slot = slot_s[j];
+    const int64_t b = slot / block_size;
+    const int o = (int)(slot - b * block_size);
+    CT* kdst = key_cache + b * blk_elems + ((int64_t)h0 * groups_per_head * block_size + o) * X;
+    CT* vdst = value_cache + b * blk_elems + (int64_t)h0 * head_size * block_size + o;
+    const CT* ksrc = ks + j * rsk;
+    const CT* vsrc = vs + j * rsv;
 #pragma unroll 4
-  for (int u = r0; u < n_groups; u += RL)
-    *reinterpret_cast<int4*>(kdst + u * kstep) = *reinterpret_cast<const int4*>(ksrc + u * X);
+    for (int u = r0; u < n_groups; u += RL)
+      *reinterpret_cast<int4*>(kdst + u * kstep) = *reinterpret_cast<const int4*>(ksrc + u * X);
 #pragma unroll 8
-  for (int e = r0; e < n; e += RL) vdst[(int64_t)e * block_size] = vsrc[e];
+    for (int e = r0; e < n; e += RL) vdst[(int64_t)e * block_size] = vsrc[e];
+    return;
+  }
+  for (int j = 0; j < TT; ++j) {
+    const int64_t slot = slot_s[j];
+    if (slot < 0) continue;
+    const int64_t b = slot / block_size;
+    const int o = (int)(slot - b * block_size);
+    CT* kdst = key_cache + b * blk_elems + ((int64_t)h0 * groups_per_head * block_size + o) * X;
+    CT* vdst = value_cache + b * blk_elems + (int64_t)h0 * head_size * block_size + o;
+    const CT* ksrc = ks + j * rsk;
+    const CT* vsrc = vs + j * rsv;
+    for (int u = threadIdx.x; u < n_groups; u += kTileThreads)
+      *reinterpret_cast<int4*>(kdst + u * kstep) = *reinterpret_cast<const int4*>(ksrc + u * X);
+#pragma unroll 4
+    for (int e = threadIdx.x; e < n; e += kTileThreads) vdst[(int64_t)e * block_size] = vsrc[e];
+  }
 }
 
 template <typename T, int KV>
@@ -231,7 +261,7 @@ static int launch_reshape(const b200pa_reshape_params_t* p, cudaStream_t stream)
     }
   }
   if (vec_ok) {
-    int threads = std::min(std::max(n / X, 32), 256);
+    int threads = std::min(std::max(2 * n / X, 32), 512);
     threads = (threads + 31) / 32 * 32;
     reshape_and_cache_vec_kernel<T, KV><<<grid, threads, 0, stream>>>(
         static_cast<const T*>(p->key), static_cast<const T*>(p->value), static_cast<CT*>(p->key_cache),

@@ -121,6 +121,29 @@ void paged_attention_v1(torch::Tensor& out, torch::Tensor& query, torch::Tensor&
   check_status(b200pa_paged_attention_v1(&a, current_stream()), &a, query, kv_cache_dtype);
 }
 
+// decode over the flash-attention cache layout [num_blocks, block_size, num_kv_heads, head_size]
+// (what flash_attn_with_kvcache does for the FLASH_ATTN backend, vllm/attention/backends/flash_attn.py:354-367)
+void paged_attention_flash(torch::Tensor& out, torch::Tensor& query, torch::Tensor& key_cache,
+                           torch::Tensor& value_cache, float scale, torch::Tensor& block_tables,
+                           torch::Tensor& seq_lens, int max_seq_len,
+                           const c10::optional<torch::Tensor>& alibi_slopes) {
+  TORCH_CHECK(key_cache.is_cuda() && value_cache.is_cuda(), "kv caches must be CUDA tensors");
+  TORCH_CHECK(key_cache.dim() == 4 && value_cache.dim() == 4 && key_cache.stride(3) == 1 && value_cache.stride(3) == 1,
+              "flash layout: key_cache / value_cache [num_blocks, block_size, num_kv_heads, head_size]");
+  TORCH_CHECK(key_cache.scalar_type() == query.scalar_type() && value_cache.scalar_type() == query.scalar_type(),
+              "flash layout: the cache has the query dtype");
+  TORCH_CHECK(key_cache.strides() == value_cache.strides(), "key_cache and value_cache must share their strides");
+  b200pa_attn_params_t a{};
+  fill_attention(a, out, query, key_cache.size(2), scale, block_tables, seq_lens, key_cache.size(1), max_seq_len,
+                 alibi_slopes, "auto", 1.0f, 0, 0, 0, 64, 0);
+  a.key_cache = key_cache.data_ptr();
+  a.value_cache = value_cache.data_ptr();
+  a.kv_block_stride = key_cache.stride(0);
+  a.kv_head_stride = key_cache.stride(2);
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
+  check_status(b200pa_paged_attention_flash(&a, key_cache.stride(1), current_stream()), &a, query, "auto");
+}
+
 // csrc/ops.h:14-30 (fork ABI: cache pointers as decimal strings + key strides)
 void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tensor& max_logits,
                         torch::Tensor& tmp_out, torch::Tensor& query, const std::string& key_cache_data_ptr_str,
@@ -467,6 +490,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   ops.def("paged_attention_v1", &paged_attention_v1,
           "Compute the attention between an input query and the cached keys/values using PagedAttention.");
   ops.def("paged_attention_v2", &paged_attention_v2, "PagedAttention V2.");
+  ops.def("paged_attention_flash", &paged_attention_flash,
+          "Decode attention over the flash-attention cache layout [num_blocks, block_size, num_kv_heads, head_size]");
   // csrc/pybind.cpp:33-38
   ops.def("context_attention_fwd", &context_attention_fwd,
           "Prefill attention of new tokens over the cached prefix (paged cache) + themselves (causal)",
