@@ -651,6 +651,59 @@ def cpu_reference_run(cfg, total_budget_s, steps, warmup, version="v2"):
     return nbytes / dt / 1e9, desc
 
 
+def host_metadata_extra():
+    """SURVEY §8 f4, host only: the reference's per-token / per-sequence Python loops that build slot_mapping and
+    block_tables (restated in oracle/metadata_ref.py from vllm/worker/model_runner.py:464-502, 543-556) timed beside
+    the vectorised builders of vllm_legacy_b200.worker.attn_metadata, on a config-2 decode step and a prefill chunk."""
+    from oracle import metadata_ref as ref
+    from vllm_legacy_b200.worker import attn_metadata as am
+    rng = random.Random(0)
+    B = 16
+    out = []
+
+    def best(fn, reps=5):
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            fn()
+            ts.append(time.perf_counter() - t0)
+        return min(ts) * 1e3
+
+    for name, lens, ctxs in (("config 2 decode step (256 seqs x 4096 ctx)", [4096] * 256, [4095] * 256),
+                             ("prefill chunk (8 seqs x 2048 new tokens over 4096 cached)", [6144] * 8, [4096] * 8)):
+        bts = [[rng.randrange(10 ** 6) for _ in range((n + B - 1) // B)] for n in lens]
+        width = max(len(b) for b in bts)
+        ms_ref = best(lambda: (ref.slot_mapping_loops(bts, ctxs, lens, B), ref.make_tensor_with_pad_loops(bts, width, 0)))
+        ms_new = best(lambda: (am.build_slot_mapping(bts, ctxs, lens, B), am.pad_block_tables(bts, width, 0)))
+        out.append({"step": name, "reference_loops_ms": round(ms_ref, 3), "vectorised_ms": round(ms_new, 3),
+                    "speedup": round(ms_ref / ms_new, 1)})
+    # steady-state decode: every step each sequence grows by one token (a new block every 16 steps); the reference
+    # rebuilds both arrays from the Python lists each step, the cache copies only what is new
+    lens = [4096 - 64] * 256
+    bts = [[rng.randrange(10 ** 6) for _ in range((n + B - 1) // B)] for n in lens]
+    cache = am.BlockTableCache(4096 // B)
+    ids = list(range(256))
+    cache.decode_step(ids, bts, lens, B)
+    t_ref = t_new = 0.0
+    for _ in range(48):
+        lens = [n + 1 for n in lens]
+        for bt, n in zip(bts, lens):
+            if (n + B - 1) // B > len(bt):
+                bt.append(rng.randrange(10 ** 6))
+        t0 = time.perf_counter()
+        ref.slot_mapping_loops(bts, [n - 1 for n in lens], lens, B)
+        ref.make_tensor_with_pad_loops(bts, max(len(b) for b in bts), 0)
+        t1 = time.perf_counter()
+        cache.decode_step(ids, bts, lens, B)
+        t2 = time.perf_counter()
+        t_ref += t1 - t0
+        t_new += t2 - t1
+    out.append({"step": "48 consecutive config-2 decode steps, per step (BlockTableCache: incremental rows)",
+                "reference_loops_ms": round(t_ref / 48 * 1e3, 3), "vectorised_ms": round(t_new / 48 * 1e3, 3),
+                "speedup": round(t_ref / t_new, 1)})
+    return out
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return None
@@ -742,6 +795,7 @@ def main():
                     cb = dict(desc)
                     cb.update({"value": round(gbps, 3), "unit": UNIT})
                     line["cpu_baseline"] = cb
+                    line.setdefault("extra", {})["host_metadata"] = host_metadata_extra()
                     if "extra" in line and isinstance(line["extra"].get("configs"), list):
                         # BASELINE configs[0] as worded: paged_attention_v1 on the vLLM CPU extension, 16 x 1024 MHA
                         c1 = dict(num_seqs=16, ctx=1024, num_heads=32, num_kv_heads=32, head_size=128, block_size=16)

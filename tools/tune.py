@@ -44,7 +44,31 @@ DEFAULTS = {"stages": 0, "evict_normal": -1, "force_simt": 0, "partition_size": 
             "split_cost": 512}
 
 
+def build_flash(name):
+    """The same shapes over the flash-attention cache layout [nb, B, H, D] (paged_attention_flash)."""
+    lens, Hq, Hkv, D, B, kvd = CONFIGS[name[:-len("_flash")]]
+    S, L = len(lens), max(lens)
+    scale = D ** -0.5
+    nblk = [(l + B - 1) // B for l in lens]
+    NB = sum(nblk) + 1
+    kv = torch.empty(2, NB, B, Hkv, D, dtype=torch.bfloat16, device=DEV).uniform_(-scale, scale)
+    q = torch.empty(S, Hq, D, dtype=torch.bfloat16, device=DEV).uniform_(-scale, scale)
+    perm = torch.randperm(NB - 1, device=DEV).to(torch.int32)
+    bt = torch.zeros(S, max(nblk), dtype=torch.int32, device=DEV)
+    o = 0
+    for i, n in enumerate(nblk):
+        bt[i, :n] = perm[o:o + n]
+        o += n
+    sl = torch.tensor(lens, dtype=torch.int32, device=DEV)
+    out = torch.empty_like(q)
+    nbytes = sum(lens) * Hkv * D * 2 * 2 + 2 * S * Hq * D * 2
+    fn = lambda: ops.paged_attention_flash(out, q, kv[0], kv[1], scale, bt, sl, L, None)
+    return fn, fn, nbytes, S
+
+
 def build(name):
+    if name.endswith("_flash"):
+        return build_flash(name)
     lens, Hq, Hkv, D, B, kvd = CONFIGS[name]
     S, L = len(lens), max(lens)
     scale = D ** -0.5
