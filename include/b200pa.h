@@ -5,8 +5,8 @@
  * module (DeepAuto-AI/vllm-legacy, vLLM 0.4.3 fork).  Plain pointers and sizes,
  * no torch types.  Every entry point names the reference interface it replaces.
  * All device entry points are asynchronous on `stream`, allocate nothing, do no
- * host synchronisation and are CUDA-graph capturable (except swap_blocks, which
- * is a host loop of async copies exactly like the reference's).
+ * host synchronisation and are CUDA-graph capturable (swap_blocks too when both
+ * sides are device-visible: it is then a gather kernel, see below).
  *
  * Return value: B200PA_OK (0) or a negative b200pa_status_t.  The PyTorch
  * binding (vllm_legacy_b200/csrc/torch_binding.cpp) maps the codes to the
@@ -300,7 +300,17 @@ int b200pa_copy_blocks(void* const* key_cache_ptrs, void* const* value_cache_ptr
  * replaces: csrc/cache.h:8-9, csrc/cache_kernels.cu:25-64.
  *   block_mapping : HOST int64 [num_pairs, 2]
  *   kind          : 0 device->device, 1 device->host, 2 host->device
- * Consecutive (src+1, dst+1) runs are merged into one cudaMemcpyAsync.
+ * When both sides are visible to the device (device memory, pinned or mapped host
+ * memory) and block_bytes % 16 == 0, the copy is ONE gather kernel per 1024 pairs:
+ * the host-resident mapping travels as kernel parameters and every (pair, slice)
+ * is copied by its own CTA with 128-bit loads/stores over NVLink-C2C / PCIe.
+ * PRECONDITION of that path: destination blocks are pairwise distinct (the block
+ * manager guarantees it, vllm/core/block_manager_v1.py swap_in/swap_out).  The
+ * reference's sequential loop gives last-writer-wins for duplicate destinations;
+ * the parallel gather leaves such a block undefined.
+ * Otherwise (pageable host memory, odd sizes, B200PA_SWAP_MEMCPY set at load):
+ * one cudaMemcpyAsync per run of consecutive (src+1, dst+1) pairs, in mapping
+ * order, i.e. the reference's semantics including duplicates.
  */
 typedef enum { B200PA_D2D = 0, B200PA_D2H = 1, B200PA_H2D = 2 } b200pa_copy_kind_t;
 

@@ -65,6 +65,8 @@ void fill_attention(b200pa_attn_params_t& a, torch::Tensor& out, torch::Tensor& 
   TORCH_CHECK(query.dim() == 3 && query.stride(2) == 1 && query.stride(1) == query.size(2),
               "query must be [num_seqs, num_heads, head_size] with contiguous heads");
   TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
+  TORCH_CHECK(out.scalar_type() == query.scalar_type() && out.numel() == query.size(0) * query.size(1) * query.size(2),
+              "out must have the query's dtype and [num_seqs, num_heads, head_size] elements");
   TORCH_CHECK(block_tables.scalar_type() == at::ScalarType::Int && seq_lens.scalar_type() == at::ScalarType::Int,
               "block_tables and seq_lens must be int32");
   TORCH_CHECK(block_tables.dim() == 2 && block_tables.stride(1) == 1 && block_tables.stride(0) == block_tables.size(1),
@@ -113,6 +115,13 @@ void paged_attention_v1(torch::Tensor& out, torch::Tensor& query, torch::Tensor&
                  kv_cache_dtype, kv_scale, tp_rank, blocksparse_local_blocks, blocksparse_vert_stride,
                  blocksparse_block_size, blocksparse_head_sliding_step);
   TORCH_CHECK(key_cache.is_cuda() && value_cache.is_cuda(), "kv caches must be CUDA tensors");
+  // a cache of the wrong element size would be reinterpreted silently (and bulk-copied with the wrong chunk size)
+  const int64_t cache_elt = kv_cache_dtype == "auto" ? query.element_size() : 1;
+  TORCH_CHECK(key_cache.element_size() == cache_elt && value_cache.element_size() == cache_elt,
+              "kv cache element size ", key_cache.element_size(), " does not match kv_cache_dtype '", kv_cache_dtype, "'");
+  TORCH_CHECK(key_cache.dim() >= 2 && value_cache.dim() >= 2 && key_cache.stride(0) == value_cache.stride(0) &&
+                  key_cache.stride(1) == value_cache.stride(1),
+              "key_cache and value_cache must share their block and head strides");
   a.key_cache = key_cache.data_ptr();
   a.value_cache = value_cache.data_ptr();
   a.kv_block_stride = key_cache.stride(0);
