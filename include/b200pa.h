@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define B200PA_ABI_VERSION 1
+#define B200PA_ABI_VERSION 2 /* 2: b200pa_prefill_params_t gained kv_scale (fp8 KV prefix) */
 
 /* CUDA stream handle (== cudaStream_t == CUstream). */
 typedef struct CUstream_st* b200pa_stream_t;
@@ -243,12 +243,17 @@ int b200pa_rotary_embedding(const b200pa_rope_params_t* p, b200pa_stream_t strea
  * Layouts:
  *   query, out     [num_tokens, num_heads, head_size]      strides (q|o)_stride_t / _h, innermost contiguous
  *   key, value     [num_tokens, num_kv_heads, head_size]   strides (k|v)_stride_t / _h, 16-byte aligned rows
- *   key_cache      [num_blocks, num_kv_heads, head_size/8, block_size, 8]   (16-bit cache, x = 8)
+ *   key_cache      [num_blocks, num_kv_heads, head_size/x, block_size, x]   x = 8 (16-bit cache) | 16 (fp8 cache)
  *   value_cache    [num_blocks, num_kv_heads, head_size, block_size]
  *   block_tables   [batch, block_table_stride] int32; start_loc, seq_lens, ctx_lens [batch] int32
- * head_size: any multiple of 8 up to 256; block_size: any power of two >= 8; dtype f16 | bf16;
- * kv_dtype must be B200PA_KV_AUTO (the reference's fp8 branch here is e5m2-bitcast-only and documented
- * as broken, vllm/attention/backends/xformers.py:301-304).
+ * head_size: any multiple of 8 up to 256 (16 with an fp8 cache); block_size: any power of two >= 8;
+ * dtype f16 | bf16.
+ * kv_dtype: B200PA_KV_AUTO (cache has the query dtype) or fp8 e4m3 / e5m2 (uint8 cache).  fp8 bytes are
+ * dequantised while the tile is staged, with the decode kernels' conversion (fp8 -> half -> float x kv_scale
+ * -> dtype, quant_utils.cuh:293-454), so prefill and decode see the same K/V values.  The reference's own
+ * fp8 branch here is an e5m2 bit-cast without a scale (prefix_prefill.py:122-123, 168-169) that its callers
+ * document as broken (vllm/attention/backends/xformers.py:301-304); kv_dtype = e5m2 with kv_scale = 1 is
+ * that behaviour, everything else is what the fork's fp8 e4m3 caches need (BASELINE config 4).
  */
 typedef struct {
   void* out;
@@ -279,6 +284,7 @@ typedef struct {
   int32_t dtype;          /* b200pa_dtype_t */
   int32_t kv_dtype;       /* b200pa_kv_dtype_t */
   float scale;            /* the reference uses 1/sqrt(head_size) (:706) */
+  float kv_scale;         /* fp8 caches only (ignored for B200PA_KV_AUTO) */
 } b200pa_prefill_params_t;
 
 int b200pa_context_attention_fwd(const b200pa_prefill_params_t* p, b200pa_stream_t stream);

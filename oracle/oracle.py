@@ -203,9 +203,32 @@ def float_to_fp8(x: float, kv_dtype: str = "fp8") -> int:
     return int(lib().oracle_float_to_fp8(ctypes.c_float(x), KV[kv_dtype]))
 
 
+def dequant_prefix_caches(k_cache_u8, v_cache_u8, dtype, kv_scale: float = 1.0, kv_dtype: str = "fp8"):
+    """fp8 paged caches (K [nb, H, D/16, B, 16], V [nb, H, D, B], uint8) -> the 16-bit caches the kernels see
+    after `scaled_convert` on load (quant_utils.cuh:293-454: fp8 -> half -> float x kv_scale -> dtype), K
+    re-laid-out to the 16-bit layout [nb, H, D/8, B, 8].  This IS the fp8 semantics of the decode kernels
+    (attention_kernels.cu:284-289, 413-419), applied to prefix-prefill."""
+    k8, v8 = _cpu(k_cache_u8).contiguous(), _cpu(v_cache_u8).contiguous()
+    assert k8.dtype == torch.uint8 and v8.dtype == torch.uint8 and k8.shape[-1] == 16
+    kd = torch.empty(k8.shape, dtype=dtype)
+    vd = torch.empty(v8.shape, dtype=dtype)
+    convert_fp8(kd, k8, kv_scale, kv_dtype)
+    convert_fp8(vd, v8, kv_scale, kv_dtype)
+    nb, h, dg, b, _ = k8.shape
+    # [nb, H, D/16, B, 16] -> token-major [nb, H, B, D] -> [nb, H, D/8, B, 8]
+    kd = kd.permute(0, 1, 3, 2, 4).reshape(nb, h, b, dg * 2, 8).permute(0, 1, 3, 2, 4).contiguous()
+    return kd, vd
+
+
 def context_attention_fwd(q, k, v, o, k_cache, v_cache, b_loc, b_start_loc, b_seq_len, b_ctx_len, max_input_len,
-                          alibi_slopes=None, sliding_window=None) -> None:
-    """Restatement of the reference's Triton prefix-prefill kernels (prefix_prefill.py:10-245, 442-681)."""
+                          alibi_slopes=None, sliding_window=None, kv_cache_dtype: str = "auto",
+                          kv_scale: float = 1.0) -> None:
+    """Restatement of the reference's Triton prefix-prefill kernels (prefix_prefill.py:10-245, 442-681).
+    uint8 caches are dequantised first (`dequant_prefix_caches`); with kv_cache_dtype "auto" they are read as
+    e5m2 without a scale, the reference kernels' own bit-cast (prefix_prefill.py:122-123, 168-169)."""
+    if k_cache.dtype == torch.uint8:
+        kvd, sc = ("fp8_e5m2", 1.0) if kv_cache_dtype == "auto" else (kv_cache_dtype, kv_scale)
+        k_cache, v_cache = dequant_prefix_caches(k_cache, v_cache, q.dtype, sc, kvd)
     for t in (q, k, v, o, k_cache, v_cache):
         assert _cpu(t).is_contiguous() and t.dtype == q.dtype
     assert k_cache.shape[-1] == 8, "16-bit cache layout (x = 8)"

@@ -254,3 +254,21 @@ def load_ref_prefix_prefill():
         return mod
     except Exception:  # noqa: BLE001 - an incompatible Triton just means "no reference run"
         return None
+
+
+def quantize_prefill_case(case, oracle, kv_dtype: str = "fp8", kv_scale: float = 1.0):
+    """Same prefill case over an fp8 KV cache: the 16-bit caches are quantised with the reference's
+    reshape_and_cache conversion (oracle.convert_fp8 = cvt_satfinite(x / kv_scale), quant_utils.cuh:456-488) and K is
+    re-laid-out to the fp8 layout [nb, H, D/16, B, 16] (x = 16).  NaN fill (stale slots) stays NaN in fp8."""
+    out = dict(case)
+    kc, vc = case["k_cache"].cpu().contiguous(), case["v_cache"].cpu().contiguous()
+    dev = case["k_cache"].device
+    nb, h, dg, b, x = kc.shape
+    assert x == 8 and dg % 2 == 0, "fp8 caches need head_size % 16 == 0"
+    k_tok = kc.permute(0, 1, 3, 2, 4).reshape(nb, h, b, dg // 2, 16).permute(0, 1, 3, 2, 4).contiguous()
+    k8 = torch.empty(k_tok.shape, dtype=torch.uint8)
+    v8 = torch.empty(vc.shape, dtype=torch.uint8)
+    oracle.convert_fp8(k8, k_tok, kv_scale, kv_dtype)
+    oracle.convert_fp8(v8, vc, kv_scale, kv_dtype)
+    out["k_cache"], out["v_cache"] = k8.to(dev), v8.to(dev)
+    return out

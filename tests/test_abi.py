@@ -38,7 +38,7 @@ def test_header_declares_the_hot_path():
 def test_library_exports_every_declared_symbol(lib):
     for s in _declared_symbols():
         assert hasattr(lib, s), f"{s} declared in include/b200pa.h but not exported"
-    assert lib.b200pa_abi_version() == 1
+    assert lib.b200pa_abi_version() == 2
 
 
 class AttnParams(ctypes.Structure):

@@ -272,3 +272,84 @@ def test_long_context_chunk(ops):
     case3["v"] = torch.full_like(case["v"], 0.5)
     c = _run(ops, case3)
     torch.testing.assert_close(c.float(), torch.full_like(c, 0.5).float(), atol=4e-3, rtol=0)
+
+
+# ---- prefix-prefill over an fp8 KV cache (dequantised while staged; SURVEY §8 f1, BASELINE config 4) -----------
+def _run_fp8(ops, case, kv_dtype, kv_scale, slopes=None, window=None):
+    out = torch.full_like(case["query"], float("nan"))
+    ops.context_attention_fwd(case["query"], case["k"], case["v"], out, case["k_cache"], case["v_cache"],
+                              case["block_table"], case["b_start_loc"], case["b_seq_len"], case["b_ctx_len"],
+                              case["max_input_len"], slopes, window, kv_dtype, kv_scale)
+    torch.cuda.synchronize()
+    return out
+
+
+def _oracle_fp8(oracle, case, kv_dtype, kv_scale, slopes=None, window=None):
+    cpu = {n: (t.cpu() if torch.is_tensor(t) else t) for n, t in case.items()}
+    exp = torch.empty_like(cpu["query"])
+    oracle.context_attention_fwd(cpu["query"], cpu["k"], cpu["v"], exp, cpu["k_cache"], cpu["v_cache"],
+                                 cpu["block_table"], cpu["b_start_loc"], cpu["b_seq_len"], cpu["b_ctx_len"],
+                                 cpu["max_input_len"], slopes, window, kv_dtype, kv_scale)
+    return exp
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("head_size", [128, 64, 96, 192])   # 128/64: tcgen05 loaders; 96/192: mma.sync staging
+@pytest.mark.parametrize("block_size", [8, 16, 32])
+@pytest.mark.parametrize("kv", [("fp8", 1.0), ("fp8_e4m3", 0.37), ("fp8_e5m2", 2.0)])
+@torch.inference_mode()
+def test_fp8_kv_prefix_vs_oracle(ops, oracle, dtype, head_size, block_size, kv):
+    """fp8 cache bytes -> T with the decode kernels' conversion, then the usual prefix attention: compare with the
+    oracle run over the dequantised cache.  Stale slots hold fp8 NaN bytes."""
+    kv_dtype, kv_scale = kv
+    case = helpers.make_prefill_case(8, 4, head_size, dtype, DEV, query_lens=[150, 1, 260, 129, 40],
+                                     ctx_lens=[130, 300, 0, 31, 7], block_size=block_size, amplitude=1.0,
+                                     seed=head_size + block_size, stale_nan=True)
+    q8 = helpers.quantize_prefill_case(case, oracle, kv_dtype, kv_scale)
+    out = _run_fp8(ops, q8, kv_dtype, kv_scale)
+    assert not torch.isnan(out).any()
+    exp = _oracle_fp8(oracle, q8, kv_dtype, kv_scale)
+    atol = 1e-3 if dtype == torch.float16 else 4e-3
+    torch.testing.assert_close(out.cpu().float(), exp.float(), atol=atol, rtol=1e-2)
+
+
+@pytest.mark.parametrize("mode", ["window", "alibi"])
+@pytest.mark.parametrize("max_q", [48, 400])   # <= 64 rows: mma.sync family; longer: tcgen05
+@torch.inference_mode()
+def test_fp8_kv_prefix_masks(ops, oracle, mode, max_q):
+    case = helpers.make_prefill_case(16, 8, 128, torch.bfloat16, DEV, batch=5, max_q=max_q, max_ctx=500,
+                                     block_size=16, amplitude=1.0, min_len=1, seed=max_q, stale_nan=True)
+    q8 = helpers.quantize_prefill_case(case, oracle, "fp8", 0.5)
+    slopes = _alibi_slopes(16) if mode == "alibi" else None
+    window = 100 if mode == "window" else 0
+    out = _run_fp8(ops, q8, "fp8", 0.5, slopes.to(DEV) if slopes is not None else None, window)
+    assert not torch.isnan(out).any()
+    exp = _oracle_fp8(oracle, q8, "fp8", 0.5, slopes, window)
+    torch.testing.assert_close(out.cpu().float(), exp.float(), atol=4e-3, rtol=1e-2)
+
+
+@torch.inference_mode()
+def test_fp8_kv_prefix_auto_is_e5m2_bitcast(ops, oracle):
+    """A uint8 cache with kv_cache_dtype "auto" is read as e5m2 without a scale — the reference Triton kernels' own
+    rule (prefix_prefill.py:122-123, 168-169); an explicit fp8 dtype + kv_scale gives the decode kernels' values."""
+    H, Hkv, D, B = 8, 2, 128, 16
+    case = helpers.make_prefill_case(H, H // Hkv, D, torch.bfloat16, DEV, query_lens=[1, 1, 140], ctx_lens=[100, 257, 31],
+                                     block_size=B, amplitude=1.0, seed=5)
+    q8 = helpers.quantize_prefill_case(case, oracle, "fp8", 0.5)
+    out = _run_fp8(ops, q8, "fp8", 0.5)
+    torch.testing.assert_close(out.cpu().float(), _oracle_fp8(oracle, q8, "fp8", 0.5).float(), atol=4e-3, rtol=1e-2)
+    q5 = helpers.quantize_prefill_case(case, oracle, "fp8_e5m2", 1.0)
+    out5 = _run_fp8(ops, q5, "auto", 1.0)
+    torch.testing.assert_close(out5.cpu().float(), _oracle_fp8(oracle, q5, "fp8_e5m2", 1.0).float(), atol=4e-3, rtol=1e-2)
+
+
+@torch.inference_mode()
+def test_fp8_kv_prefix_rejects_bad_shapes(ops):
+    case = helpers.make_prefill_case(4, 1, 24, torch.float16, DEV, query_lens=[5], ctx_lens=[9], block_size=16)
+    k8 = torch.zeros(case["k_cache"].shape[0], 4, 24 // 8, 16, 8, dtype=torch.uint8, device=DEV)  # x = 8 bytes: not an fp8 layout
+    v8 = torch.zeros_like(case["v_cache"], dtype=torch.uint8)
+    out = torch.empty_like(case["query"])
+    with pytest.raises(RuntimeError):
+        ops.context_attention_fwd(case["query"], case["k"], case["v"], out, k8, v8, case["block_table"],
+                                  case["b_start_loc"], case["b_seq_len"], case["b_ctx_len"], case["max_input_len"],
+                                  None, None, "fp8", 1.0)

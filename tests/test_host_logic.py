@@ -152,6 +152,39 @@ def test_backend_impl_mixed_prefill_decode(recorder):
     assert name == "context_attention_fwd" and args[8].tolist() == [5, 3] and args[9].tolist() == [0, 0]
 
 
+def test_backend_fp8_cache_prefill_paths(recorder):
+    """fp8 KV cache: a prompt with a cached prefix hands the cache dtype and kv_scale to the prefix kernel (which
+    dequantises while staging); a prompt without one never reads the cache (xformers.py:291-300) and runs on a dummy
+    16-bit cache with kv_cache_dtype "auto"."""
+    Hq, Hkv, D, B, nb = 8, 2, 64, 16, 8
+    impl = B200PagedAttentionBackend.get_impl_cls()(Hq, D, 0.125, Hkv, None, None, "fp8")
+    kv_cache = torch.zeros(*B200PagedAttentionBackend.get_kv_cache_shape(nb, B, Hkv, D), dtype=torch.uint8)
+    meta = B200PagedAttentionBackend.make_metadata(
+        num_prefills=1, num_prefill_tokens=5, num_decode_tokens=1, slot_mapping=torch.arange(6),
+        seq_lens=[21, 7], seq_lens_tensor=torch.tensor([21, 7], dtype=torch.int32), max_query_len=5,
+        max_prefill_seq_len=21, max_decode_seq_len=7, query_start_loc=torch.tensor([0, 5, 6], dtype=torch.int32),
+        context_lens_tensor=torch.tensor([16, 6], dtype=torch.int32),
+        block_tables=torch.arange(4, dtype=torch.int32).view(2, 2), use_cuda_graph=False)
+    q = torch.zeros(6, Hq * D, dtype=torch.bfloat16)
+    kv = torch.zeros(6, Hkv * D, dtype=torch.bfloat16)
+    impl.forward(q, kv, kv.clone(), kv_cache, meta, 0.5)
+    names = [c[0] for c in recorder.calls]
+    assert names == ["reshape_and_cache", "context_attention_fwd", "paged_attention_v1"]
+    pf = recorder.calls[1][1]
+    assert pf[4].dtype == torch.uint8 and pf[4].shape[-1] == 16   # K cache view with x = 16
+    assert pf[13] == "fp8" and pf[14] == 0.5
+    recorder.calls.clear()
+    meta2 = B200PagedAttentionBackend.make_metadata(
+        num_prefills=1, num_prefill_tokens=5, num_decode_tokens=0, slot_mapping=torch.arange(5),
+        seq_lens=[5], seq_lens_tensor=torch.tensor([5], dtype=torch.int32), max_query_len=5, max_prefill_seq_len=5,
+        max_decode_seq_len=0, query_start_loc=torch.tensor([0, 5], dtype=torch.int32),
+        context_lens_tensor=torch.zeros(1, dtype=torch.int32), block_tables=torch.zeros(1, 0, dtype=torch.int32))
+    impl.forward(q[:5], kv[:5], kv[:5].clone(), kv_cache, meta2, 0.5)
+    assert [c[0] for c in recorder.calls] == ["reshape_and_cache", "context_attention_fwd"]
+    pf = recorder.calls[1][1]
+    assert pf[4].dtype == torch.bfloat16 and pf[13] == "auto"
+
+
 def test_shard_heads_matches_reference_rules():
     """vllm/config.py:320-333."""
     s = [shard_heads(64, 8, 8, r) for r in range(8)]

@@ -344,3 +344,30 @@ def test_oracle_context_attention_vs_dense(oracle, dtype, mode):
     ref = helpers.ref_context_attention(case, slopes, window)
     tol = {torch.float16: 2e-3, torch.bfloat16: 1e-2, torch.float32: 1e-5}[dtype]
     torch.testing.assert_close(out.float(), ref, atol=tol, rtol=1e-2)
+
+
+def test_fp8_prefix_cache_dequant_layout(oracle):
+    """quantize_prefill_case (x = 8 -> fp8 x = 16 layout) and oracle.dequant_prefix_caches (back) are inverse
+    re-layouts, and the values are exactly convert_fp8(convert_fp8(x)) element by element."""
+    from tests import helpers
+    case = helpers.make_prefill_case(4, 2, 32, torch.bfloat16, "cpu", query_lens=[3, 5], ctx_lens=[20, 9],
+                                     block_size=8, amplitude=1.0)
+    q8 = helpers.quantize_prefill_case(case, oracle, "fp8", 0.5)
+    assert q8["k_cache"].dtype == torch.uint8 and q8["k_cache"].shape[-1] == 16
+    kd, vd = oracle.dequant_prefix_caches(q8["k_cache"], q8["v_cache"], torch.bfloat16, 0.5, "fp8")
+    assert kd.shape == case["k_cache"].shape and vd.shape == case["v_cache"].shape
+    for orig, deq in ((case["k_cache"], kd), (case["v_cache"], vd)):
+        tmp = torch.empty(orig.shape, dtype=torch.uint8)
+        oracle.convert_fp8(tmp, orig.contiguous(), 0.5, "fp8")
+        want = torch.empty_like(orig)
+        oracle.convert_fp8(want, tmp, 0.5, "fp8")
+        assert torch.equal(want.view(torch.int16), deq.view(torch.int16))
+    # and the oracle accepts the uint8 caches directly
+    out = torch.empty_like(case["query"])
+    oracle.context_attention_fwd(case["query"], case["k"], case["v"], out, q8["k_cache"], q8["v_cache"],
+                                 case["block_table"], case["b_start_loc"], case["b_seq_len"], case["b_ctx_len"],
+                                 case["max_input_len"], None, None, "fp8", 0.5)
+    ref = torch.empty_like(case["query"])
+    oracle.context_attention_fwd(case["query"], case["k"], case["v"], ref, kd, vd, case["block_table"],
+                                 case["b_start_loc"], case["b_seq_len"], case["b_ctx_len"], case["max_input_len"])
+    assert torch.equal(out.view(torch.int16), ref.view(torch.int16))

@@ -119,9 +119,13 @@ def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: 
                           k_cache: torch.Tensor, v_cache: torch.Tensor, b_loc: torch.Tensor,
                           b_start_loc: torch.Tensor, b_seq_len: torch.Tensor, b_ctx_len: torch.Tensor,
                           max_input_len: int, alibi_slopes: Optional[torch.Tensor] = None,
-                          sliding_window: Optional[int] = None) -> None:
+                          sliding_window: Optional[int] = None, kv_cache_dtype: str = "auto",
+                          kv_scale: float = 1.0) -> None:
+    # kv_cache_dtype / kv_scale are additions (the reference wrapper has neither): an fp8 (uint8) cache is
+    # dequantised while it is staged, like the decode kernels do; "auto" with a uint8 cache keeps the
+    # reference kernels' e5m2 bit-cast (prefix_prefill.py:122-123).
     vllm_ops.context_attention_fwd(q, k, v, o, k_cache, v_cache, b_loc, b_start_loc, b_seq_len, b_ctx_len,
-                                   max_input_len, alibi_slopes, sliding_window)
+                                   max_input_len, alibi_slopes, sliding_window, kv_cache_dtype, kv_scale)
 
 
 # cache ops

@@ -171,7 +171,7 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
         if prefill_meta := attn_metadata.prefill_metadata:
             output[:num_prefill_tokens] = self._forward_prefill(
                 query[:num_prefill_tokens], key[:num_prefill_tokens], value[:num_prefill_tokens],
-                key_cache, value_cache, prefill_meta)
+                key_cache, value_cache, prefill_meta, kv_scale)
 
         if decode_meta := attn_metadata.decode_metadata:
             assert kv_cache is not None, "decode needs the paged KV cache"
@@ -187,12 +187,14 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
                 blocksparse_head_sliding_step=bs.get("head_sliding_step", 0))
         return output.view(-1, self.num_heads * self.head_size)
 
-    def _forward_prefill(self, query, key, value, key_cache, value_cache, meta) -> torch.Tensor:
+    def _forward_prefill(self, query, key, value, key_cache, value_cache, meta, kv_scale=1.0) -> torch.Tensor:
         """Prompt run (xformers.py:291-318).  With a cached prefix the reference calls
         PagedAttention.forward_prefix; without one (no cache yet, or empty block tables) it runs plain causal
         attention through xformers — here that is the same kernel with every context length 0."""
         no_prefix = key_cache is None or meta.block_tables is None or meta.block_tables.numel() == 0
+        kv_cache_dtype = self.kv_cache_dtype
         if no_prefix:
+            kv_cache_dtype = "auto"  # the dummy cache below has the query dtype
             # plain causal attention over the new tokens only: the (possibly fp8) cache is not read (xformers.py:291-300)
             dev, nseq = query.device, meta.num_prefills
             key_cache = torch.empty(1, self.num_kv_heads, self.head_size // 8, 8, 8, dtype=query.dtype, device=dev)
@@ -204,4 +206,4 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
             block_tables, context_lens, seq_lens = meta.block_tables, meta.context_lens_tensor, meta.seq_lens_tensor
         return PagedAttention.forward_prefix(query, key, value, key_cache, value_cache, block_tables,
                                              meta.query_start_loc, seq_lens, context_lens, meta.max_query_len,
-                                             self.alibi_slopes, self.sliding_window)
+                                             self.alibi_slopes, self.sliding_window, kv_cache_dtype, kv_scale)

@@ -101,14 +101,16 @@ class PagedAttention:
     def forward_prefix(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor,
                        value_cache: torch.Tensor, block_tables: torch.Tensor, query_start_loc: torch.Tensor,
                        seq_lens_tensor: torch.Tensor, context_lens: torch.Tensor, max_query_len: int,
-                       alibi_slopes: Optional[torch.Tensor], sliding_window: Optional[int]) -> torch.Tensor:
+                       alibi_slopes: Optional[torch.Tensor], sliding_window: Optional[int],
+                       kv_cache_dtype: str = "auto", kv_scale: float = 1.0) -> torch.Tensor:
         """Prompt tokens against their cached prefix + themselves (paged_attn.py:185-216): one launch of the
         sm_100a prefix-prefill kernel (csrc/prefill_tc.cu / prefill.cu).  `query_start_loc` has batch + 1 entries;
         the kernel wants each sequence's first row, i.e. all but the last."""
         out = torch.empty_like(query)
         first_rows = query_start_loc[:-1]
         ops.context_attention_fwd(query, key, value, out, key_cache, value_cache, block_tables, first_rows,
-                                  seq_lens_tensor, context_lens, max_query_len, alibi_slopes, sliding_window)
+                                  seq_lens_tensor, context_lens, max_query_len, alibi_slopes, sliding_window,
+                                  kv_cache_dtype, kv_scale)
         return out
 
     @staticmethod

@@ -23,6 +23,8 @@ def context_attention_fwd(q: torch.Tensor,
                           b_ctx_len: torch.Tensor,
                           max_input_len: int,
                           alibi_slopes: Optional[torch.Tensor] = None,
-                          sliding_window: Optional[int] = None) -> None:
+                          sliding_window: Optional[int] = None,
+                          kv_cache_dtype: str = "auto",
+                          kv_scale: float = 1.0) -> None:
     ops.context_attention_fwd(q, k, v, o, k_cache, v_cache, b_loc, b_start_loc, b_seq_len, b_ctx_len,
-                              max_input_len, alibi_slopes, sliding_window)
+                              max_input_len, alibi_slopes, sliding_window, kv_cache_dtype, kv_scale)

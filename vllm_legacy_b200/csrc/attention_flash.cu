@@ -324,6 +324,10 @@ static int launch_flash_stages(const AttnKernelParams& kp, int num_seqs, cudaStr
     if (kp.num_stages == 3 || (three_fit && kp.num_stages != 2)) return launch_flash_one<T, D, B, NG, 3>(kp, num_seqs, stream);
   }
   if constexpr (two_possible) return launch_flash_one<T, D, B, NG, 2>(kp, num_seqs, stream);
+  // block 32 with head sizes 224 / 256: two 2 x 32-token stages per warp exceed 227 KiB; a single stage per warp
+  // still overlaps across the four warps of the CTA
+  if constexpr (!two_possible && flash_smem_bytes(D, B, NG, 1) <= kFlashSmemPerSM - kFlashReserved)
+    return launch_flash_one<T, D, B, NG, 1>(kp, num_seqs, stream);
   return 1;
 }
 

@@ -156,7 +156,44 @@ __global__ void __launch_bounds__(kThreads, (DP <= 128 && MT == 1) ? 3 : (DP <= 
   auto issue = [&](int it, int buf) {
     const uint32_t kb = kv_smem + buf * G::STAGE;
     const uint32_t vb = kb + G::KBYTES;
-    if (it < n_ctx) {
+    if (it < n_ctx && p.kv_dtype != B200PA_KV_AUTO) {
+      // fp8 cache (x = 16): K chunk [D/16][B][16] bytes, V chunk [D][B] bytes.  Same destinations as below, but
+      // through registers: 128-bit / 64-bit loads, fp8 -> T (x kv_scale, the decode kernels' conversion), 128-bit
+      // shared stores.  Plain stores: the __syncthreads that publishes the cp.async tiles publishes these too.
+      const int t0 = (c_first + it) * BN;
+      const uint8_t* kc8 = static_cast<const uint8_t*>(p.k_cache) + (int64_t)kv_head * p.kc_head_stride;
+      const uint8_t* vc8 = static_cast<const uint8_t*>(p.v_cache) + (int64_t)kv_head * p.vc_head_stride;
+      {
+        const int t = tid % BN;
+        const int kpos = t0 + t;
+        const bool tv = kpos < ctx_len;
+        const int64_t phys = tv ? table[kpos >> bshift] : 0;
+        const uint8_t* src = kc8 + phys * p.kc_block_stride + (kpos & (B - 1)) * 16;
+        const uint32_t dst = kb + t * G::KPITCH;
+#pragma unroll
+        for (int c = tid / BN; c < DP / 16; c += kThreads / BN) {
+          const bool ok = tv && c * 16 < D;
+          int4 raw = make_int4(0, 0, 0, 0);
+          if (ok) raw = ld_nc_v4(src + (int64_t)c * B * 16);
+          const uint4 zero = make_uint4(0, 0, 0, 0);
+          st_shared_v4(dst + c * 32, ok ? fp8x8_to_t<T>(p.kv_dtype, make_uint2(raw.x, raw.y), p.kv_scale) : zero);
+          st_shared_v4(dst + c * 32 + 16, ok ? fp8x8_to_t<T>(p.kv_dtype, make_uint2(raw.z, raw.w), p.kv_scale) : zero);
+        }
+      }
+#pragma unroll 4
+      for (int u = tid; u < DP * BN / 8; u += kThreads) {
+        const int d = u / (BN / 8);
+        const int tt = (u - d * (BN / 8)) * 8;
+        const int kpos = t0 + tt;
+        const bool ok = kpos < ctx_len && d < D;
+        uint4 w = make_uint4(0, 0, 0, 0);
+        if (ok) {
+          const int64_t phys = table[kpos >> bshift];
+          w = fp8x8_to_t<T>(p.kv_dtype, ld_nc_v2(vc8 + phys * p.vc_block_stride + (int64_t)d * B + (kpos & (B - 1))), p.kv_scale);
+        }
+        st_shared_v4(vb + d * G::VPITCH + tt * 2, w);
+      }
+    } else if (it < n_ctx) {
       const int t0 = (c_first + it) * BN;
       {  // K: unit (d-group g, token t) of the paged chunk [D/8][B][8] -> row t, column group g
         const int t = tid % BN;
@@ -471,8 +508,10 @@ extern "C" int b200pa_context_attention_fwd(const b200pa_prefill_params_t* a, b2
   using namespace b200pa;
   if (!a) return B200PA_ERR_INVALID_ARG;
   if (a->dtype != B200PA_F16 && a->dtype != B200PA_BF16) return B200PA_ERR_INPUT_DTYPE;
-  if (a->kv_dtype != B200PA_KV_AUTO) return B200PA_ERR_KV_DTYPE;
+  const bool fp8 = a->kv_dtype == B200PA_KV_FP8_E4M3 || a->kv_dtype == B200PA_KV_FP8_E5M2;
+  if (a->kv_dtype != B200PA_KV_AUTO && !fp8) return B200PA_ERR_KV_DTYPE;
   if (a->head_size <= 0 || a->head_size > 256 || a->head_size % 8 != 0) return B200PA_ERR_HEAD_SIZE;
+  if (fp8 && a->head_size % 16 != 0) return B200PA_ERR_HEAD_SIZE;  // x = 16 bytes of one token per K run
   int bshift = 0;
   while ((1 << bshift) < a->block_size) ++bshift;
   if (a->block_size < 8 || (1 << bshift) != a->block_size) return B200PA_ERR_BLOCK_SIZE;
@@ -487,7 +526,8 @@ extern "C" int b200pa_context_attention_fwd(const b200pa_prefill_params_t* a, b2
   // 16-byte cp.async rows for k / v / caches, 32-bit accesses for q / out
   if (mis(a->key, 16) || mis(a->value, 16) || mis(a->key_cache, 16) || mis(a->value_cache, 16) || mis(a->query, 4) ||
       mis(a->out, 4) || a->k_stride_t % 8 || a->k_stride_h % 8 || a->v_stride_t % 8 || a->v_stride_h % 8 ||
-      a->kc_block_stride % 8 || a->kc_head_stride % 8 || a->vc_block_stride % 8 || a->vc_head_stride % 8 ||
+      a->kc_block_stride % (fp8 ? 16 : 8) || a->kc_head_stride % (fp8 ? 16 : 8) || a->vc_block_stride % 8 ||
+      a->vc_head_stride % 8 ||
       a->q_stride_t % 2 || a->q_stride_h % 2 || a->o_stride_t % 2 || a->o_stride_h % 2)
     return B200PA_ERR_INVALID_ARG;
 
@@ -522,6 +562,8 @@ extern "C" int b200pa_context_attention_fwd(const b200pa_prefill_params_t* a, b2
   kp.block_shift = bshift;
   kp.sliding_window = a->sliding_window > 0 ? a->sliding_window : 0;
   kp.scale_log2 = a->scale * kLog2e;
+  kp.kv_dtype = a->kv_dtype;
+  kp.kv_scale = fp8 ? a->kv_scale : 1.0f;
   // tcgen05 + TMEM family first (128-row CTAs; head sizes <= 128 that are multiples of 16); the mma.sync family
   // takes short queries and every other shape.  B200PA_PREFILL_TC=0/1 forces the choice (tuning / tests).
   static const int tc_knob = [] { const char* e = std::getenv("B200PA_PREFILL_TC"); return e ? std::atoi(e) : -1; }();

@@ -669,7 +669,30 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
       for (int h = lw; h < 2; h += LW) {
         const int kt = lane + 32 * h;
         const uint32_t dst = kb + kt * 16;  // (token t, d-group g) -> g * (BN * 16) + t * 16
-        if (it < n_ctx) {
+        if (it < n_ctx && p.kv_dtype != B200PA_KV_AUTO) {
+          // fp8 cache: the token's 16-byte runs [D/16][B][16] are dequantised in registers (the decode kernels'
+          // conversion) and stored as two 16-byte core-matrix rows each.  Plain stores: the fence.proxy.async +
+          // mbarrier arrive that publish the cp.async tiles publish these too.
+          const int phys = h ? e1 : e0;
+          const int kpos = (c_first + it) * BN + kt;
+          const uint8_t* src = static_cast<const uint8_t*>(p.k_cache) + (int64_t)kv_head * p.kc_head_stride +
+                               (int64_t)max(phys, 0) * p.kc_block_stride + (kpos & (B - 1)) * 16;
+          int4 raw[DP / 16];
+#pragma unroll
+          for (int c = 0; c < DP / 16; ++c) {
+            raw[c] = make_int4(0, 0, 0, 0);
+            if (phys >= 0 && c * 16 < D) raw[c] = ld_nc_v4(src + (int64_t)c * B * 16);
+          }
+#pragma unroll
+          for (int c = 0; c < DP / 16; ++c) {
+            const bool ok = phys >= 0 && c * 16 < D;
+            const uint4 zero = make_uint4(0, 0, 0, 0);
+            st_shared_v4(dst + (2 * c) * (BN * 16),
+                         ok ? fp8x8_to_t<T>(p.kv_dtype, make_uint2(raw[c].x, raw[c].y), p.kv_scale) : zero);
+            st_shared_v4(dst + (2 * c + 1) * (BN * 16),
+                         ok ? fp8x8_to_t<T>(p.kv_dtype, make_uint2(raw[c].z, raw[c].w), p.kv_scale) : zero);
+          }
+        } else if (it < n_ctx) {
           const int phys = h ? e1 : e0;
           const int kpos = (c_first + it) * BN + kt;
           const T* src = kc + (int64_t)max(phys, 0) * p.kc_block_stride + (kpos & (B - 1)) * 8;
@@ -803,7 +826,35 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
     auto load_v = [&](int it, int phys) {
       if (it >= n_tiles) return;
       const uint32_t vb = v_smem + (it % G::VSTAGES) * G::VBYTES;
-      if (it < n_ctx) {
+      if (it < n_ctx && p.kv_dtype != B200PA_KV_AUTO) {
+        // fp8 cache: 8 tokens of one d row are 8 bytes; dequantise in registers, zero the tokens behind ctx_len
+        const int kpos = (c_first + it) * BN + vg;
+        const int nvalid = min(8, max(0, ctx_len - kpos));
+        const uint8_t* src = static_cast<const uint8_t*>(p.v_cache) + (int64_t)kv_head * p.vc_head_stride +
+                             (int64_t)max(phys, 0) * p.vc_block_stride + (kpos & (B - 1));
+        const uint32_t dst = vb + (vg >> 3) * (DP * 16);
+        constexpr int kRows = DP / (4 * LW);  // rows of this lane
+        constexpr int kBatch = 8;
+        const int d0 = (lane >> 3) + 4 * lw;
+#pragma unroll 1
+        for (int r0 = 0; r0 < kRows; r0 += kBatch) {
+          uint2 raw[kBatch];
+#pragma unroll
+          for (int r = 0; r < kBatch; ++r) {
+            const int d = d0 + (r0 + r) * 4 * LW;
+            raw[r] = make_uint2(0, 0);
+            if (phys >= 0 && d < D && nvalid > 0) raw[r] = ld_nc_v2(src + (int64_t)d * B);
+          }
+#pragma unroll
+          for (int r = 0; r < kBatch; ++r) {
+            const int d = d0 + (r0 + r) * 4 * LW;
+            const bool ok = phys >= 0 && d < D && nvalid > 0;
+            uint4 w = make_uint4(0, 0, 0, 0);
+            if (ok) w = keep_first_elems(fp8x8_to_t<T>(p.kv_dtype, raw[r], p.kv_scale), nvalid);
+            st_shared_v4(dst + d * 16, w);
+          }
+        }
+      } else if (it < n_ctx) {
         const int kpos = (c_first + it) * BN + vg;
         const int nbytes = 2 * min(8, max(0, ctx_len - kpos));
         const T* src = vc + (int64_t)max(phys, 0) * p.vc_block_stride + (kpos & (B - 1));
@@ -1037,6 +1088,7 @@ int launch_prefill_tc(const PrefillParams& kp, int batch, int max_query_len, int
   const int d = kp.head_size;
   if (d % 16 != 0) return 1;
   static const int ws_knob = [] { const char* e = std::getenv("B200PA_PREFILL_WS"); return e ? std::atoi(e) : kWsDefault; }();
+  if (!ws_knob && kp.kv_dtype != B200PA_KV_AUTO) return 1;  // fp8 staging lives in the warp-specialised kernel's loaders
   if (ws_knob) {
     if (dtype == B200PA_F16) {
       if (d <= 64) return prefill_tc::launch_ws<__half, 64>(kp, batch, max_query_len, stream);

@@ -425,7 +425,8 @@ void context_attention_fwd(torch::Tensor& q, torch::Tensor& k, torch::Tensor& v,
                            torch::Tensor& k_cache, torch::Tensor& v_cache, torch::Tensor& b_loc,
                            torch::Tensor& b_start_loc, torch::Tensor& b_seq_len, torch::Tensor& b_ctx_len,
                            int max_input_len, const c10::optional<torch::Tensor>& alibi_slopes,
-                           const c10::optional<int64_t>& sliding_window) {
+                           const c10::optional<int64_t>& sliding_window, const std::string& kv_cache_dtype,
+                           float kv_scale) {
   TORCH_CHECK(q.is_cuda() && k.is_cuda() && v.is_cuda() && o.is_cuda() && k_cache.is_cuda() && v_cache.is_cuda() &&
                   b_loc.is_cuda() && b_start_loc.is_cuda() && b_seq_len.is_cuda() && b_ctx_len.is_cuda(),
               "b200pa context_attention_fwd: tensors must be on a CUDA device (there is no CPU path)");
@@ -481,9 +482,20 @@ void context_attention_fwd(torch::Tensor& q, torch::Tensor& k, torch::Tensor& v,
   p.sliding_window = sliding_window.has_value() ? static_cast<int>(*sliding_window) : 0;
   p.dtype = scalar_dtype(q);
   const int cdt = scalar_dtype(k_cache);
-  TORCH_CHECK(cdt == p.dtype && k_cache.size(4) * k_cache.element_size() == 16 && v_cache.scalar_type() == k_cache.scalar_type(),
-              "context_attention_fwd: the paged cache must have the query dtype (kv_cache_dtype=\"auto\", x = 8)");
-  p.kv_dtype = B200PA_KV_AUTO;
+  TORCH_CHECK(k_cache.size(4) * k_cache.element_size() == 16 && v_cache.scalar_type() == k_cache.scalar_type(),
+              "context_attention_fwd: k_cache must be [nb, H, D/x, B, x] with x = 16 bytes, v_cache of the same dtype");
+  if (cdt == B200PA_U8) {
+    // uint8 cache = fp8.  With kv_cache_dtype "auto" (the reference wrapper has no such argument) the bytes are
+    // read as e5m2 without a scale, which is what the reference's Triton kernels do (prefix_prefill.py:122-123).
+    p.kv_dtype = kv_cache_dtype == "auto" ? B200PA_KV_FP8_E5M2 : parse_kv_dtype(kv_cache_dtype);
+    p.kv_scale = kv_cache_dtype == "auto" ? 1.0f : kv_scale;
+    TORCH_CHECK(p.kv_dtype != B200PA_KV_AUTO, "Unsupported data type of kv cache: ", kv_cache_dtype);
+  } else {
+    TORCH_CHECK(cdt == p.dtype && kv_cache_dtype == "auto",
+                "context_attention_fwd: a 16-bit paged cache must have the query dtype and kv_cache_dtype=\"auto\"");
+    p.kv_dtype = B200PA_KV_AUTO;
+    p.kv_scale = 1.0f;
+  }
   p.scale = 1.0f / std::sqrt(static_cast<float>(p.head_size));
   const int rc = b200pa_context_attention_fwd(&p, current_stream());
   if (rc == B200PA_ERR_HEAD_SIZE) TORCH_CHECK(false, "Unsupported head size: ", p.head_size);
@@ -507,7 +519,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           pybind11::arg("q"), pybind11::arg("k"), pybind11::arg("v"), pybind11::arg("o"), pybind11::arg("k_cache"),
           pybind11::arg("v_cache"), pybind11::arg("b_loc"), pybind11::arg("b_start_loc"), pybind11::arg("b_seq_len"),
           pybind11::arg("b_ctx_len"), pybind11::arg("max_input_len"), pybind11::arg("alibi_slopes") = pybind11::none(),
-          pybind11::arg("sliding_window") = pybind11::none());
+          pybind11::arg("sliding_window") = pybind11::none(), pybind11::arg("kv_cache_dtype") = "auto",
+          pybind11::arg("kv_scale") = 1.0f);
   ops.def("rotary_embedding", &rotary_embedding, "Apply GPT-NeoX or GPT-J style rotary embedding to query and key");
   ops.def("batched_rotary_embedding", &batched_rotary_embedding,
           "Apply GPT-NeoX or GPT-J style rotary embedding to query and key (batched cos/sin offsets)");
