@@ -52,7 +52,8 @@ typedef enum {
   B200PA_ERR_INPUT_DTYPE = -4, /* "Unsupported input type of kv cache: " quant_utils.cuh:538    */
   B200PA_ERR_INVALID_ARG = -5, /* null pointer / negative size / misaligned cache               */
   B200PA_ERR_CUDA = -6,        /* a CUDA runtime call failed: see b200pa_last_cuda_error()      */
-  B200PA_ERR_DEVICE_COMBINATION = -7 /* "Invalid device combination"   cache_kernels.cu:41-43   */
+  B200PA_ERR_DEVICE_COMBINATION = -7, /* "Invalid device combination"   cache_kernels.cu:41-43   */
+  B200PA_ERR_SCRATCH_LIMIT = -8 /* b200pa_paged_attention_static_scratch: the problem exceeds the static scratch */
 } b200pa_status_t;
 
 /*
@@ -110,6 +111,30 @@ typedef struct {
 
 int b200pa_paged_attention_v1(const b200pa_attn_params_t* p, b200pa_stream_t stream);
 int b200pa_paged_attention_v2(const b200pa_attn_params_t* p, b200pa_stream_t stream);
+
+/*
+ * paged_attention_static_scratch — split-K decode attention that allocates nothing
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same inputs, outputs and arithmetic as b200pa_paged_attention_v1 on the TMA + mma.sync kernel family (dtype
+ * f16 | bf16, block_size 16 | 32, dense, kv_dtype auto | fp8); exp_sums / max_logits / tmp_out /
+ * max_num_partitions of the parameter block are ignored.  Where v1 keeps its split-K partials and arrival
+ * counters in a per-device workspace that its first call cudaMallocs, this entry point keeps them in ONE
+ * file-scope `static __device__` array inside the library (csrc/attention_noalloc.cu): it calls no cudaMalloc,
+ * cudaFree or allocating library routine, on any call.  Every GPU that loads the library holds the array
+ * (B200PA_STATIC_SCRATCH_BYTES + 4 * B200PA_STATIC_SCRATCH_COUNTERS bytes) until exit.
+ * Limits — beyond them the call returns B200PA_ERR_SCRATCH_LIMIT and launches nothing:
+ *   num_seqs * num_kv_heads * ceil(group / (group <= 8 ? 8 : 16))   <= B200PA_STATIC_SCRATCH_COUNTERS
+ *   2 * num_seqs * num_heads * (head_size * 2 + 8)                  <= B200PA_STATIC_SCRATCH_BYTES
+ * (group = num_heads / num_kv_heads; i.e. two context splits of the whole batch must fit.  Larger batches fill
+ * the GPU without a split: use b200pa_paged_attention_v1 / _v2 for them.)
+ * All calls share the array and it keeps the last call's contents: the counters are cleared on `stream` at the
+ * start of every call (a memset node under capture), the partials are written before they are read.  Calls that
+ * OVERLAP on the GPU (different streams, concurrently replayed graphs) race on it — serialise them.
+ */
+#define B200PA_STATIC_SCRATCH_BYTES (8 * 1024 * 1024)
+#define B200PA_STATIC_SCRATCH_COUNTERS 4096
+int b200pa_paged_attention_static_scratch(const b200pa_attn_params_t* p, b200pa_stream_t stream);
 
 /*
  * paged_attention_flash — decode over the flash-attention cache layout

@@ -63,6 +63,26 @@ def _params(**kw):
     return p
 
 
+def test_static_scratch_entry_point_validation(lib):
+    """b200pa_paged_attention_static_scratch (no reference counterpart): argument classes and the static-scratch
+    limits are checked before any CUDA call, so they answer without a GPU."""
+    f = lib.b200pa_paged_attention_static_scratch
+    f.restype = ctypes.c_int
+    assert f(None, None) == -5
+    assert f(ctypes.byref(_params()), None) == -5           # null pointers
+    assert f(ctypes.byref(_params(block_size=8)), None) == -2
+    assert f(ctypes.byref(_params(dtype=2)), None) == -4    # fp32 queries: not in the mma family
+    assert f(ctypes.byref(_params(kv_dtype=7)), None) == -3
+    fake = {n: 4096 for n in ("out", "query", "key_cache", "value_cache", "block_tables", "seq_lens")}
+    strides = dict(q_stride=8 * 128, kv_block_stride=2 * 128 * 16, kv_head_stride=128 * 16)
+    # 4097 sequences x 1 KV head: one arrival counter too many
+    assert f(ctypes.byref(_params(num_seqs=4097, num_heads=8, num_kv_heads=1, max_seq_len=4096, **fake, **strides)), None) == -8
+    # 2 x [2048 seqs, 8 heads] x (128 x 2 + 8) bytes = 8.25 MiB of partials: over the 8 MiB array
+    assert f(ctypes.byref(_params(num_seqs=2048, num_heads=8, num_kv_heads=1, max_seq_len=4096, **fake, **strides)), None) == -8
+    lib.b200pa_status_string.restype = ctypes.c_char_p
+    assert b"static scratch" in lib.b200pa_status_string(-8)
+
+
 def test_attention_argument_validation(lib):
     """Error classes of attention_kernels.cu:764 (head size), :801 (block size), quant_utils.cuh:564/538."""
     f = lib.b200pa_paged_attention_v1

@@ -64,7 +64,7 @@ def build(force=False, verbose=False):
     hdrs = _headers()
     jobs = []
     for name in ("cache.cu", "cache_flash.cu", "rope.cu", "prefill.cu", "prefill_tc.cu", "attention.cu", "attention_simt.cu", "attention_mma.cu",
-                 "attention_flash.cu"):
+                 "attention_flash.cu", "attention_noalloc.cu"):
         src = os.path.join(CSRC, name)
         obj = os.path.join(OBJ, name + ".o")
         jobs.append((["nvcc", *NVCC_FLAGS, "-c", src, "-o", obj], obj, [src, *hdrs]))

@@ -650,6 +650,8 @@ extern "C" const char* b200pa_status_string(int status) {
     case B200PA_ERR_INVALID_ARG: return "invalid argument";
     case B200PA_ERR_CUDA: return "CUDA error";
     case B200PA_ERR_DEVICE_COMBINATION: return "Invalid device combination";
+    case B200PA_ERR_SCRATCH_LIMIT:
+      return "problem exceeds the static scratch of b200pa_paged_attention_static_scratch (limits in include/b200pa.h)";
     default: return "unknown status";
   }
 }
