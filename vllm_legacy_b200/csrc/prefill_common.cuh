@@ -25,6 +25,7 @@ struct PrefillParams {
   float scale_log2;  // scale * log2(e)
   int kv_dtype;      // B200PA_KV_AUTO: 16-bit cache (x = 8); fp8: uint8 cache (x = 16), dequantised while staging
   float kv_scale;
+  int use_tma;       // prefill_tc.cu: full cached-prefix tiles staged by TMA (set by the launcher when a tensor map exists)
 };
 
 // ---- fp8 cache bytes -> T while staging a cached K/V tile -------------------------------------------

@@ -22,7 +22,10 @@
 //                                          every MMA + 1 warp that stages V; the roles only meet on mbarriers;
 //   context_attention_tc_kernel            the same pipeline with all four warps doing everything (two CTA-wide
 //                                          barriers per tile); kept selectable with B200PA_PREFILL_WS=0.
+#include <cuda.h>  // CUtensorMap (types only; the encoder is fetched from the driver at run time)
+
 #include <cstdlib>
+#include <cstring>
 #include <type_traits>
 
 #include "prefill_common.cuh"
@@ -156,6 +159,27 @@ __device__ __forceinline__ void tc_st32(uint32_t taddr, const uint32_t (&r)[32])
       "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
       : "memory");
 }
+// ---- TMA staging of full cached-prefix tiles ----------------------------------------------------------
+// expect_tx without an arrival: the loader still arrives once per tile at the top of that tile's iteration (as it
+// does for cp.async tiles), the phase completes when the arrivals AND the announced bytes are in.
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// 1-D bulk copy (SASS UBLKCP): one contiguous run of the paged K chunk
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+// 4-D tensor-map copy (SASS UTMALDG): box {8 tokens, DP rows} of the paged V chunk [nb][Hkv][D][B] lands as DP rows
+// of 16 bytes = one K-major core-matrix column of the P.V B operand; rows >= head_size are zero-filled by the TMA.
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* tmap, int c0, int c1, int c2, int c3, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];" ::"r"(dst),
+      "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar)
+      : "memory");
+}
+
 __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
@@ -568,6 +592,11 @@ constexpr int kWsProducerWarps = 3;  // warp 4 NQ: MMA issue; 4 NQ + 1: V copies
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// Asynchronous arrive: fires when every cp.async this thread has issued so far has completed (counts as one of the
+// barrier's expected arrivals).  The loader never waits for a tile to land: it issues, posts this, and moves on.
+__device__ __forceinline__ void cp_async_arrive(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
 
 // NQ = query heads per CTA.  With NQ = 2 the CTA serves two query heads of one GQA group against the SAME staged
 // K/V tiles (the L2 -> shared-memory copies, not the math, bound the NQ = 1 kernel: removing them took it from
@@ -577,7 +606,7 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 // its last tile and the earlier tile sees the up to two extra causal tiles fully masked (p = 0).
 template <typename T, int DP, int NQ, bool ROWS>
 __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
-    context_attention_ws_kernel(const __grid_constant__ PrefillParams p) {
+    context_attention_ws_kernel(const __grid_constant__ PrefillParams p, const __grid_constant__ CUtensorMap vmap) {
   using G = Geometry<DP>;
   constexpr int QBYTES = NQ * G::QBYTES;
   constexpr int TMEM_COLS = NQ * 256;
@@ -615,6 +644,10 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
   const int j_end = (min(q_len, m0 + CTA_ROWS) + BN - 1) / BN;
   const int n_ctx = max(0, c_end - c_first);
   const int n_tiles = n_ctx + (j_end - j_first);
+  // Cached-prefix tiles that lie completely below ctx_len are staged by TMA (bulk copies for K, tensor-map boxes for
+  // V); the last, partial prefix tile and the new-token tiles keep the cp.async path (it zero-fills behind ctx_len).
+  const bool use_tma = p.use_tma != 0;
+  auto tma_tile = [&](int it) -> bool { return use_tma && it < n_ctx && (c_first + it + 1) * BN <= ctx_len; };
 
   const uint32_t q_smem = smem_u32(smem);
   const uint32_t k_smem = q_smem + QBYTES;
@@ -637,9 +670,10 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
       mbar_init(p_full + 8 * i, 128);
     }
     for (int s = 0; s < G::VSTAGES; ++s) mbar_init(pv_done + 8 * s, 1);
-    for (int s = 0; s < G::VSTAGES; ++s) mbar_init(v_full + 8 * s, LW);
-    mbar_init(k_full, LW);
-    mbar_init(k_full + 8, LW);
+    // every lane of every loader warp arrives once per tile (asynchronously for cp.async tiles)
+    for (int s = 0; s < G::VSTAGES; ++s) mbar_init(v_full + 8 * s, 32 * LW);
+    mbar_init(k_full, 32 * LW);
+    mbar_init(k_full + 8, 32 * LW);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   tc_fence_before();
@@ -729,27 +763,97 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
         }
       }
     }
-    load_k(0, k_entry(0, 0), k_entry(0, 1));
-    cp_async_commit();  // G: Q, K(0)
-    load_k(1, k_entry(1, 0), k_entry(1, 1));
-    cp_async_commit();  // G: K(1)
+    // ---- TMA path: a full prefix tile is (BN / run) x (D / 8) contiguous runs of run x 16 bytes, run = min(B, BN)
+    // tokens of one d-group of one block ([D/8][B][8] chunk): one bulk copy each, this warp issues its 1/LW of them.
+    const int rshift = min(bshift, 6);
+    const int run_tok = 1 << rshift;
+    const int DGv = D >> 3;                       // d-groups that exist (D % 16 == 0)
+    const int Cw = ((BN >> rshift) * DGv) / LW;   // copies per tile and loader warp
+    const uint32_t run_bytes = (uint32_t)run_tok * 16u;
+    constexpr int KJ = 4;                         // ceil(max Cw / 32): B = 8, D = 128, LW = 1
+    auto k_tma_entries = [&](int it, int (&ent)[KJ]) {
+      const int t0 = (c_first + it) * BN;
+#pragma unroll
+      for (int j = 0; j < KJ; ++j) {
+        const int i = lw * Cw + lane + 32 * j;
+        ent[j] = (lane + 32 * j < Cw) ? table[(t0 + (i / DGv) * run_tok) >> bshift] : 0;
+      }
+    };
+    auto issue_k_tma = [&](int it, const int (&ent)[KJ]) {
+      const uint32_t kb = k_smem + (it & 1) * G::KBYTES;
+      const uint32_t bar = k_full + 8 * (it & 1);
+      const int t0 = (c_first + it) * BN;
+      if (lane == 0) mbar_expect_tx(bar, (uint32_t)Cw * run_bytes);
+      __syncwarp();
+#pragma unroll
+      for (int j = 0; j < KJ; ++j) {
+        if (lane + 32 * j < Cw) {
+          const int i = lw * Cw + lane + 32 * j;
+          const int r = i / DGv, g = i - r * DGv;
+          const int tok = t0 + r * run_tok;
+          const T* src = kc + (int64_t)ent[j] * p.kc_block_stride + (int64_t)g * B * 8 + (tok & (B - 1)) * 8;
+          bulk_g2s(kb + g * (BN * 16) + (r * run_tok) * 16, src, run_bytes, bar);
+        }
+      }
+    };
+    if (use_tma && DGv < DG) {
+      // d-groups behind head_size are never written by the bulk copies: zero them once in both K stages (Q's padded
+      // columns are zero too, but 0 x stale NaN bits would still poison S)
+      for (int u = lane + 32 * lw; u < 2 * (DG - DGv) * BN; u += 32 * LW) {
+        const int st = u / ((DG - DGv) * BN), rem = u - st * ((DG - DGv) * BN);
+        st_shared_v4(k_smem + st * G::KBYTES + DGv * (BN * 16) + rem * 16, make_uint4(0, 0, 0, 0));
+      }
+      fence_proxy_async();
+    }
+    auto stage_k = [&](int it, int e0, int e1) {  // prologue tiles: entries fetched inline
+      if (it < n_tiles && tma_tile(it)) {
+        int ent[KJ];
+        k_tma_entries(it, ent);
+        issue_k_tma(it, ent);
+      } else {
+        load_k(it, e0, e1);
+      }
+    };
+    // A tile is announced by an arrive of every lane on its k_full barrier, posted right after the lane has issued
+    // its share and never waited for: cp.async tiles use the asynchronous arrive (fires when the lane's copies have
+    // landed), fp8 tiles (plain shared stores) a proxy fence + arrive, TMA tiles an arrive next to the expect_tx.
+    // (With a synchronous wait + arrive per tile the announce of a landed tile sat behind the ~1000-clock issue of the
+    // next one and the MMA warp waited ~590 of every 2450 clocks for it: profiles/r02_prefill_phase_trace*.log.)
+    const bool fp8_cache = p.kv_dtype != B200PA_KV_AUTO;
+    auto announce_k = [&](int it) {
+      if (it >= n_tiles) return;
+      const uint32_t bar = k_full + 8 * (it & 1);
+      if (tma_tile(it) || (fp8_cache && it < n_ctx)) {
+        if (it == 0) {  // Q's cp.async copies ride on tile 0: a plain arrive must not overtake them
+          cp_async_commit();
+          cp_async_wait<0>();
+        }
+        fence_proxy_async();
+        mbar_arrive(bar);
+      } else {
+        cp_async_arrive(bar);
+      }
+    };
+    stage_k(0, k_entry(0, 0), k_entry(0, 1));  // (Q rides on K(0)'s announce)
+    announce_k(0);
+    stage_k(1, k_entry(1, 0), k_entry(1, 1));
+    announce_k(1);
     int ek0 = k_entry(2, 0), ek1 = k_entry(2, 1);  // for the refill of iteration 0
 
-
-    for (int it = 0; it < n_tiles; ++it) {
-      cp_async_wait<1>();  // Q and K(it) have landed (this lane's share)
-      fence_proxy_async();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(k_full + 8 * (it & 1));
-      // K(it+2) goes into the stage QK(it) reads: wait for the last head's QK(it)
-      if (it + 2 < n_tiles) {
-        mbar_wait_relaxed(s_full + 16 * (NQ - 1) + 8 * (it & 1), (it >> 1) & 1);
-        load_k(it + 2, ek0, ek1);
-      }
-      cp_async_commit();
+    for (int it = 0; it + 2 < n_tiles; ++it) {
+      // K(it+2) goes into the stage QK(it) reads: wait for the last head's QK(it).  That wait also implies every
+      // loader lane has arrived for tile it, so an expect_tx below lands in tile it+2's phase of the barrier.
+      const bool t2 = tma_tile(it + 2);
+      int ent[KJ] = {0, 0, 0, 0};
+      if (t2) k_tma_entries(it + 2, ent);  // block-table loads fly during the wait below
+      mbar_wait_relaxed(s_full + 16 * (NQ - 1) + 8 * (it & 1), (it >> 1) & 1);
+      if (t2) issue_k_tma(it + 2, ent);
+      else load_k(it + 2, ek0, ek1);
+      announce_k(it + 2);
       ek0 = k_entry(it + 3, 0);
       ek1 = k_entry(it + 3, 1);
     }
+    cp_async_commit();
     cp_async_wait<0>();
   } else if (warp == MMA_WARP) {
     // ================================ MMA issuer ================================
@@ -771,7 +875,9 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
     };
 
 
+    // (fence.proxy.async on the consumer side too: the loaders' asynchronous arrives carry no fence of their own)
     mbar_wait_relaxed(k_full, 0);  // Q, K(0)
+    fence_proxy_async();
     tc_fence_after();
     if (elect_one()) issue_qk(0);
     __syncwarp();
@@ -783,6 +889,7 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
       if (it + 1 < n_tiles) {
         mbar_wait_relaxed(k_full + 8 * ((it + 1) & 1), ((it + 1) >> 1) & 1);
         B200PA_TRACE(it, 5);
+        fence_proxy_async();
         tc_fence_after();
         if (elect_one()) issue_qk(it + 1);
         __syncwarp();
@@ -790,6 +897,7 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
       B200PA_TRACE(it, 6);
       // V(it) has landed (V loader) and P(it) is in TMEM (softmax warps): O += P(it) V(it)
       mbar_wait_relaxed(v_full + 8 * (it % G::VSTAGES), (it / G::VSTAGES) & 1);
+      fence_proxy_async();
       B200PA_TRACE(it, 8);
 #pragma unroll
       for (int jq = 0; jq < NQ; ++jq) {
@@ -879,24 +987,57 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
         }
       }
     };
-    load_v(0, v_entry(0));
-    cp_async_commit();
-    load_v(1, v_entry(1));
-    cp_async_commit();
-    int ev = v_entry(2);
-    for (int it = 0; it < n_tiles; ++it) {
-      cp_async_wait<1>();  // V(it) landed (this lane's share)
-      fence_proxy_async();
+    // ---- TMA path: a full prefix tile is BN / 8 boxes {8 tokens, DP rows} of the paged V chunk, one per lane
+    // (this warp issues boxes lw, lw + LW, ...); each lands as one 16-byte column block [DP][16 B] of the stage.
+    constexpr int VBOX = (BN / 8) / LW;  // boxes per tile and loader warp
+    auto v_tma_entry = [&](int it) -> int {
+      const int kpos = (c_first + it) * BN + (lw + LW * lane) * 8;
+      return lane < VBOX ? table[kpos >> bshift] : 0;
+    };
+    auto issue_v_tma = [&](int it, int phys) {
+      const uint32_t vb = v_smem + (it % G::VSTAGES) * G::VBYTES;
+      const uint32_t bar = v_full + 8 * (it % G::VSTAGES);
+      if (lane == 0) mbar_expect_tx(bar, (uint32_t)(VBOX * DP * 16));
       __syncwarp();
-      if (lane == 0) mbar_arrive(v_full + 8 * (it % G::VSTAGES));
-      // V(it+2) goes into the stage PV(it-1) read
-      if (it + 2 < n_tiles) {
-        if (it >= 1) mbar_wait_relaxed(pv_done + 8 * ((it - 1) % G::VSTAGES), ((it - 1) / G::VSTAGES) & 1);
-        load_v(it + 2, ev);
+      if (lane < VBOX) {
+        const int tg = lw + LW * lane;
+        const int kpos = (c_first + it) * BN + tg * 8;
+        tma_load_4d(vb + tg * (DP * 16), &vmap, kpos & (B - 1), 0, kv_head, phys, bar);
       }
-      cp_async_commit();
+    };
+    auto stage_v = [&](int it) {  // prologue tiles
+      if (it < n_tiles && tma_tile(it)) issue_v_tma(it, v_tma_entry(it));
+      else load_v(it, v_entry(it));
+    };
+    const bool fp8_cache = p.kv_dtype != B200PA_KV_AUTO;
+    auto announce_v = [&](int it) {  // see the K loader
+      if (it >= n_tiles) return;
+      const uint32_t bar = v_full + 8 * (it % G::VSTAGES);
+      if (tma_tile(it)) {
+        mbar_arrive(bar);
+      } else if (fp8_cache && it < n_ctx) {
+        fence_proxy_async();
+        mbar_arrive(bar);
+      } else {
+        cp_async_arrive(bar);
+      }
+    };
+    stage_v(0);
+    announce_v(0);
+    stage_v(1);
+    announce_v(1);
+    int ev = v_entry(2);
+    for (int it = 0; it + 2 < n_tiles; ++it) {
+      // V(it+2) goes into the stage PV(it-1) read (its completion implies every loader lane arrived for tile it-1)
+      const bool t2 = tma_tile(it + 2);
+      const int et = t2 ? v_tma_entry(it + 2) : 0;  // the block-table load flies during the wait below
+      if (it >= 1) mbar_wait_relaxed(pv_done + 8 * ((it - 1) % G::VSTAGES), ((it - 1) / G::VSTAGES) & 1);
+      if (t2) issue_v_tma(it + 2, et);
+      else load_v(it + 2, ev);
+      announce_v(it + 2);
       ev = v_entry(it + 3);
     }
+    cp_async_commit();
     cp_async_wait<0>();
   } else {
     // ================================ softmax warps: thread = query row ================================
@@ -1028,9 +1169,73 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
   }
 }
 
+// Tensor map of the paged V cache for the TMA loader: dims (innermost first) {B tokens, D rows, Hkv, blocks}, box
+// {8, DP, 1, 1}, no swizzle, zero fill for rows >= D.  The encoder is a driver entry point fetched once through the
+// runtime (no link-time dependency on libcuda).  Returns false when the driver has no encoder or rejects the layout
+// (strides that are not 16-byte multiples): the kernel then keeps its cp.async loaders.
+typedef CUresult (*TensorMapEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                           const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                           CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                           CUtensorMapFloatOOBfill);
+static TensorMapEncodeTiledFn tensor_map_encoder() {
+  static const TensorMapEncodeTiledFn fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      f = nullptr;
+    (void)cudaGetLastError();
+    return reinterpret_cast<TensorMapEncodeTiledFn>(f);
+  }();
+  return fn;
+}
+static bool make_v_tensor_map(const PrefillParams& kp, int dtype, int dp, CUtensorMap* map) {
+  // Developer knob, default OFF: measured on B200 (profiles/r02_prefill_tma_vs_cpasync.log) this staging is SLOWER
+  // than the cp.async loader warps (513 vs 833 TFLOP/s on llama8b_chunk2k_ctx4k): 72 TMA instructions per tile, and
+  // the {8 tokens x DP rows} V boxes fetch one 32-byte sector per 16 bytes used (ncu: 6.44 GB through TMA for 4.29 GB
+  // of K+V).  Parity is green with it on (396 prefill tests).  B200PA_PREFILL_TMA=1 enables it.
+  static const bool off = [] { const char* e = std::getenv("B200PA_PREFILL_TMA"); return !(e && std::atoi(e) == 1); }();
+  if (off || kp.kv_dtype != B200PA_KV_AUTO) return false;
+  TensorMapEncodeTiledFn enc = tensor_map_encoder();
+  if (!enc) return false;
+  const cuuint64_t B = 1ull << kp.block_shift;
+  // one-entry cache: a model calls this once per layer with the same geometry and a different base pointer
+  struct Key { const void* ptr; int64_t hs, bs; int d, hkv, bshift, dtype, dp; };
+  static thread_local Key last_key{};
+  static thread_local CUtensorMap last_map;
+  static thread_local bool last_ok = false;
+  Key key;
+  std::memset(&key, 0, sizeof(key));
+  key.ptr = kp.v_cache; key.hs = kp.vc_head_stride; key.bs = kp.vc_block_stride; key.d = kp.head_size;
+  key.hkv = kp.num_kv_heads; key.bshift = kp.block_shift; key.dtype = dtype; key.dp = dp;
+  if (last_ok && std::memcmp(&key, &last_key, sizeof(Key)) == 0) {
+    *map = last_map;
+    return true;
+  }
+  const cuuint64_t dims[4] = {B, (cuuint64_t)kp.head_size, (cuuint64_t)kp.num_kv_heads, 1ull << 24};
+  const cuuint64_t strides[3] = {B * 2, (cuuint64_t)kp.vc_head_stride * 2, (cuuint64_t)kp.vc_block_stride * 2};
+  const cuuint32_t box[4] = {8, (cuuint32_t)dp, 1, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  if (kp.vc_head_stride <= 0 || kp.vc_block_stride <= 0 || strides[0] % 16 || strides[1] % 16 || strides[2] % 16)
+    return false;
+  const CUresult rc = enc(map, dtype == B200PA_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
+                          const_cast<void*>(kp.v_cache), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (rc != CUDA_SUCCESS) return false;
+  last_key = key;
+  last_map = *map;
+  last_ok = true;
+  return true;
+}
+
 template <typename T, int DP, int NQ, bool ROWS>
-static int launch_ws_nq(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
+static int launch_ws_nq(const PrefillParams& kp_in, int batch, int max_query_len, int dtype, cudaStream_t stream) {
   using G = Geometry<DP>;
+  PrefillParams kp = kp_in;
+  alignas(64) CUtensorMap vmap;
+  std::memset(&vmap, 0, sizeof(vmap));
+  kp.use_tma = make_v_tensor_map(kp, dtype, DP, &vmap) ? 1 : 0;
   auto kernel = context_attention_ws_kernel<T, DP, NQ, ROWS>;
   constexpr int kCtaRows = ROWS ? NQ * kBM : kBM;
   constexpr int kSmem = NQ * G::QBYTES + 2 * G::KBYTES + G::VSTAGES * G::VBYTES + 256;
@@ -1042,7 +1247,7 @@ static int launch_ws_nq(const PrefillParams& kp, int batch, int max_query_len, c
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   dim3 grid(kp.num_heads / (ROWS ? 1 : NQ), (max_query_len + kCtaRows - 1) / kCtaRows, batch);
-  kernel<<<grid, NQ * 128 + 32 + 64 * NQ, kSmem, stream>>>(kp);
+  kernel<<<grid, NQ * 128 + 32 + 64 * NQ, kSmem, stream>>>(kp, vmap);
   B200PA_CUDA_CHECK(cudaGetLastError());
   return B200PA_OK;
 }
@@ -1051,13 +1256,13 @@ static int launch_ws_nq(const PrefillParams& kp, int batch, int max_query_len, c
 // consecutive row tiles of one head when the prompts are longer than one tile.  B200PA_PREFILL_NQ (developer knob):
 // 1 = one tile per CTA, 3 = row pairs even where head pairs apply.
 template <typename T, int DP>
-static int launch_ws(const PrefillParams& kp, int batch, int max_query_len, cudaStream_t stream) {
+static int launch_ws(const PrefillParams& kp, int batch, int max_query_len, int dtype, cudaStream_t stream) {
   static const int nq_knob = [] { const char* e = std::getenv("B200PA_PREFILL_NQ"); return e ? std::atoi(e) : 0; }();
   const int group = kp.num_heads / kp.num_kv_heads;
-  if (nq_knob == 1) return launch_ws_nq<T, DP, 1, false>(kp, batch, max_query_len, stream);
-  if (group % 2 == 0 && nq_knob != 3) return launch_ws_nq<T, DP, 2, false>(kp, batch, max_query_len, stream);
-  if (max_query_len > kBM || nq_knob == 3) return launch_ws_nq<T, DP, 2, true>(kp, batch, max_query_len, stream);
-  return launch_ws_nq<T, DP, 1, false>(kp, batch, max_query_len, stream);
+  if (nq_knob == 1) return launch_ws_nq<T, DP, 1, false>(kp, batch, max_query_len, dtype, stream);
+  if (group % 2 == 0 && nq_knob != 3) return launch_ws_nq<T, DP, 2, false>(kp, batch, max_query_len, dtype, stream);
+  if (max_query_len > kBM || nq_knob == 3) return launch_ws_nq<T, DP, 2, true>(kp, batch, max_query_len, dtype, stream);
+  return launch_ws_nq<T, DP, 1, false>(kp, batch, max_query_len, dtype, stream);
 }
 
 template <typename T, int DP>
@@ -1091,11 +1296,11 @@ int launch_prefill_tc(const PrefillParams& kp, int batch, int max_query_len, int
   if (!ws_knob && kp.kv_dtype != B200PA_KV_AUTO) return 1;  // fp8 staging lives in the warp-specialised kernel's loaders
   if (ws_knob) {
     if (dtype == B200PA_F16) {
-      if (d <= 64) return prefill_tc::launch_ws<__half, 64>(kp, batch, max_query_len, stream);
-      if (d <= 128) return prefill_tc::launch_ws<__half, 128>(kp, batch, max_query_len, stream);
+      if (d <= 64) return prefill_tc::launch_ws<__half, 64>(kp, batch, max_query_len, dtype, stream);
+      if (d <= 128) return prefill_tc::launch_ws<__half, 128>(kp, batch, max_query_len, dtype, stream);
     } else if (dtype == B200PA_BF16) {
-      if (d <= 64) return prefill_tc::launch_ws<__nv_bfloat16, 64>(kp, batch, max_query_len, stream);
-      if (d <= 128) return prefill_tc::launch_ws<__nv_bfloat16, 128>(kp, batch, max_query_len, stream);
+      if (d <= 64) return prefill_tc::launch_ws<__nv_bfloat16, 64>(kp, batch, max_query_len, dtype, stream);
+      if (d <= 128) return prefill_tc::launch_ws<__nv_bfloat16, 128>(kp, batch, max_query_len, dtype, stream);
     }
     return 1;
   }
