@@ -2,6 +2,8 @@
 // (prefill.cu: mma.sync; prefill_tc.cu: tcgen05 + TMEM).
 #pragma once
 
+#include <type_traits>
+
 #include "attention_common.cuh"
 
 namespace b200pa {
@@ -31,15 +33,25 @@ struct PrefillParams {
 // ---- fp8 cache bytes -> T while staging a cached K/V tile -------------------------------------------
 // Same arithmetic as the decode kernels' scaled_convert (quant_utils.cuh:293-454): fp8 -> half (exact) -> float
 // x kv_scale -> T (round to nearest even).  8 bytes in, one 16-byte shared-memory row piece out.
+// Two bytes at a time (cvt.rn.f16x2.e?m?x2, two f16 -> f32, two fmul.rn, one packed round): the same operations per
+// element as fp8_dequant, so the results are bit-identical, in about half the instructions.
+template <typename T, int KV>
+__device__ __forceinline__ uint32_t fp8x2_to_t(uint32_t two_bytes, float scale) {
+  const __half2_raw hr = __nv_cvt_fp8x2_to_halfraw2(static_cast<__nv_fp8x2_storage_t>(two_bytes & 0xffffu), fp8_interp<KV>());
+  const float2 f = __half22float2(__half2(hr));
+  const float lo = __fmul_rn(f.x, scale), hi = __fmul_rn(f.y, scale);
+  if constexpr (std::is_same<T, __half>::value) {
+    const __half2 h = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&h);
+  } else {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&h);
+  }
+}
 template <typename T, int KV>
 __device__ __forceinline__ uint4 fp8x8_to_t(uint2 b, float scale) {
-  union { T e[8]; uint4 v; } o;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    o.e[i] = fp8_dequant<KV, T>((uint8_t)(b.x >> (8 * i)), scale);
-    o.e[4 + i] = fp8_dequant<KV, T>((uint8_t)(b.y >> (8 * i)), scale);
-  }
-  return o.v;
+  return make_uint4(fp8x2_to_t<T, KV>(b.x, scale), fp8x2_to_t<T, KV>(b.x >> 16, scale),
+                    fp8x2_to_t<T, KV>(b.y, scale), fp8x2_to_t<T, KV>(b.y >> 16, scale));
 }
 template <typename T>
 __device__ __forceinline__ uint4 fp8x8_to_t(int kv, uint2 b, float scale) {

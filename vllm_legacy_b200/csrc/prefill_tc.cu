@@ -95,6 +95,25 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity)
       "r"(parity)
       : "memory");
 }
+// The MMA-issue warp is the critical path of the warp-specialised kernel (every tensor-pipe instruction goes through
+// it): a tight poll (B200PA_PREFILL_MMA_SPIN=1 at build time) measured no gain over the relaxed wait (period 2208 vs 2202 clocks), so the back-off stays.
+// Alternating the two heads' (independent) MMA chains instead of issuing each head's chain back to back measured
+// slightly SLOWER (871 vs 890 TFLOP/s, period 2288 vs 2208 clocks; profiles/r02_prefill_experiments.log): the ~30
+// clocks every tcgen05.mma costs on top of its math time (QK N64: 62-70, PV N128: ~94) are per instruction, not a
+// dependent-issue latency.  Kept as a build-time knob, default off.
+#ifndef B200PA_PREFILL_INTERLEAVE
+#define B200PA_PREFILL_INTERLEAVE 0
+#endif
+#ifndef B200PA_PREFILL_MMA_SPIN
+#define B200PA_PREFILL_MMA_SPIN 0
+#endif
+__device__ __forceinline__ void mbar_wait_mma(uint32_t bar, uint32_t parity) {
+#if B200PA_PREFILL_MMA_SPIN
+  mbar_wait(bar, parity);
+#else
+  mbar_wait_relaxed(bar, parity);
+#endif
+}
 // MMA completion -> mbarrier (implies tcgen05.fence::before_thread_sync)
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -862,6 +881,21 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
     constexpr uint32_t idesc_pv_mn = make_idesc<T>(BM, DP, 1);
     auto issue_qk = [&](int it) {  // S_j(it & 1) = Q_j K(it)^T for every head j of the CTA
       const uint32_t kb = k_smem + (it & 1) * G::KBYTES;
+#if B200PA_PREFILL_INTERLEAVE
+      // the heads' accumulator chains are independent: alternate them, so that an MMA never queues right behind the
+      // one it accumulates onto (and both heads consume one K slice back to back)
+#pragma unroll
+      for (int ks = 0; ks < DP / 16; ++ks) {
+        const uint64_t b = make_desc(kb + ks * 2 * (BN * 16), BN * 16, 128);
+#pragma unroll
+        for (int jq = 0; jq < NQ; ++jq) {
+          const uint64_t a = make_desc(q_smem + jq * G::QBYTES + ks * 2 * (BM * 16), BM * 16, 128);
+          tc_mma(tmem_base + jq * 256 + (it & 1) * BN, a, b, idesc_qk, ks > 0 ? 1u : 0u);
+        }
+      }
+#pragma unroll
+      for (int jq = 0; jq < NQ; ++jq) tc_commit(s_full + 16 * jq + 8 * (it & 1));
+#else
 #pragma unroll
       for (int jq = 0; jq < NQ; ++jq) {
 #pragma unroll
@@ -872,11 +906,12 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
         }
         tc_commit(s_full + 16 * jq + 8 * (it & 1));
       }
+#endif
     };
 
 
     // (fence.proxy.async on the consumer side too: the loaders' asynchronous arrives carry no fence of their own)
-    mbar_wait_relaxed(k_full, 0);  // Q, K(0)
+    mbar_wait_mma(k_full, 0);  // Q, K(0)
     fence_proxy_async();
     tc_fence_after();
     if (elect_one()) issue_qk(0);
@@ -887,7 +922,7 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
       const bool is_ctx = it < n_ctx;
       const uint32_t vb = v_smem + (it % G::VSTAGES) * G::VBYTES;
       if (it + 1 < n_tiles) {
-        mbar_wait_relaxed(k_full + 8 * ((it + 1) & 1), ((it + 1) >> 1) & 1);
+        mbar_wait_mma(k_full + 8 * ((it + 1) & 1), ((it + 1) >> 1) & 1);
         B200PA_TRACE(it, 5);
         fence_proxy_async();
         tc_fence_after();
@@ -896,12 +931,31 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
       }
       B200PA_TRACE(it, 6);
       // V(it) has landed (V loader) and P(it) is in TMEM (softmax warps): O += P(it) V(it)
-      mbar_wait_relaxed(v_full + 8 * (it % G::VSTAGES), (it / G::VSTAGES) & 1);
+      mbar_wait_mma(v_full + 8 * (it % G::VSTAGES), (it / G::VSTAGES) & 1);
       fence_proxy_async();
       B200PA_TRACE(it, 8);
+#if B200PA_PREFILL_INTERLEAVE
+#pragma unroll
+      for (int jq = 0; jq < NQ; ++jq) mbar_wait_mma(p_full + 16 * jq + 8 * (it & 1), (it >> 1) & 1);
+      tc_fence_after();
+      if (elect_one()) {
+#pragma unroll
+        for (int kk = 0; kk < BN / 16; ++kk) {
+          const uint64_t b = make_desc(vb + kk * 2 * (DP * 16), DP * 16, 128);
+#pragma unroll
+          for (int jq = 0; jq < NQ; ++jq)
+            tc_mma_ts(tmem_base + jq * 256 + 2 * BN, tmem_base + jq * 256 + (it & 1) * BN + kk * 8, b,
+                      is_ctx ? idesc_pv_k : idesc_pv_mn, (it > 0 || kk > 0) ? 1u : 0u);
+        }
+        tc_commit(pv_done + 8 * (it % G::VSTAGES));  // covers every head's PV(it)
+      }
+      __syncwarp();
+      B200PA_TRACE(it, 9);
+      B200PA_TRACE(it, 10);
+#else
 #pragma unroll
       for (int jq = 0; jq < NQ; ++jq) {
-        mbar_wait_relaxed(p_full + 16 * jq + 8 * (it & 1), (it >> 1) & 1);
+        mbar_wait_mma(p_full + 16 * jq + 8 * (it & 1), (it >> 1) & 1);
         tc_fence_after();
         if (elect_one()) {
 #pragma unroll
@@ -915,6 +969,7 @@ __global__ void __launch_bounds__(NQ * 128 + 32 + 64 * NQ, NQ == 1 ? 2 : 1)
         __syncwarp();
         B200PA_TRACE(it, 9 + jq);
       }
+#endif
     }
   } else if (warp >= V_WARP) {
     const int lw = warp - V_WARP;
