@@ -153,7 +153,7 @@ def ragged_lens(n=64, lo=128, hi=131072, seed=0):
     return lens
 
 
-def make_decode_case(dev, lens, Hq, Hkv, D, B, kvd="auto", seed=0, spare_blocks=0):
+def make_decode_case(dev, lens, Hq, Hkv, D, B, kvd="auto", seed=0, spare_blocks=0, dtype=torch.bfloat16):
     """Paged KV cache resident in HBM whose block tables are a random permutation of DISTINCT physical blocks (the
     working set equals the algorithmic bytes; the reference benchmark's 1024 reused blocks would sit in L2)."""
     from vllm_legacy_b200.attention.ops.paged_attn import PagedAttention
@@ -162,7 +162,8 @@ def make_decode_case(dev, lens, Hq, Hkv, D, B, kvd="auto", seed=0, spare_blocks=
     scale = float(D ** -0.5)
     nblk = [(l + B - 1) // B for l in lens]
     NB = sum(nblk) + S + spare_blocks
-    cdt = torch.uint8 if kvd != "auto" else torch.bfloat16
+    cdt = torch.uint8 if kvd != "auto" else dtype
+    eb = torch.empty(0, dtype=dtype).element_size()
     kv_cache = torch.empty(PagedAttention.get_kv_cache_shape(NB, B, Hkv, D), dtype=cdt, device=dev)
     if kvd != "auto":
         kv_cache.random_(0, 120, generator=g)  # finite e4m3 codes
@@ -178,7 +179,7 @@ def make_decode_case(dev, lens, Hq, Hkv, D, B, kvd="auto", seed=0, spare_blocks=
             block_tables[i, :n] = perm[o:o + n]
             o += n
     seq_lens = torch.tensor(lens, dtype=torch.int32, device=dev)
-    q = torch.empty(S, Hq, D, dtype=torch.bfloat16, device=dev).uniform_(-scale, scale, generator=g)
+    q = torch.empty(S, Hq, D, dtype=dtype, device=dev).uniform_(-scale, scale, generator=g)
     key_cache, value_cache = PagedAttention.split_kv_cache(kv_cache, Hkv, D)
     P = (L + 511) // 512
     return dict(kv_cache=kv_cache, key_cache=key_cache, value_cache=value_cache, block_tables=block_tables,
@@ -187,10 +188,14 @@ def make_decode_case(dev, lens, Hq, Hkv, D, B, kvd="auto", seed=0, spare_blocks=
                 tmp_out=torch.empty(S, Hq, P, D, dtype=q.dtype, device=dev),
                 exp_sums=torch.empty(S, Hq, P, dtype=torch.float32, device=dev),
                 max_logits=torch.empty(S, Hq, P, dtype=torch.float32, device=dev),
-                nbytes=algorithmic_bytes(S, L, Hq, Hkv, D, 1 if kvd != "auto" else 2, total_tokens=sum(lens)))
+                nbytes=algorithmic_bytes(S, L, Hq, Hkv, D, 1 if kvd != "auto" else eb, eb, total_tokens=sum(lens)))
 
 
-def attention_call(ops, c, version="v2"):
+def attention_call(ops, c, version="v2", blocksparse=None):
+    if blocksparse is not None:  # (local_blocks, vert_stride, block_size, head_sliding_step), tp_rank 0
+        return lambda: ops.paged_attention_v2(c["out"], c["exp_sums"], c["max_logits"], c["tmp_out"], c["q"],
+                                              c["key_cache"], c["value_cache"], c["Hkv"], c["scale"], c["block_tables"],
+                                              c["seq_lens"], c["B"], c["L"], None, c["kvd"], 1.0, 0, *blocksparse)
     if version == "v1":
         return lambda: ops.paged_attention_v1(c["out"], c["q"], c["key_cache"], c["value_cache"], c["Hkv"], c["scale"],
                                               c["block_tables"], c["seq_lens"], c["B"], c["L"], None, c["kvd"], 1.0)
@@ -456,12 +461,13 @@ def configs_extra(ops, dev, peak):
         d.update(kw)
         out.append(d)
 
-    def attn(name, workload, lens, Hq, Hkv, D, B, kvd="auto", versions=("v2",), small=False, iters=20):
-        c = make_decode_case(dev, lens, Hq, Hkv, D, B, kvd)
+    def attn(name, workload, lens, Hq, Hkv, D, B, kvd="auto", versions=("v2",), small=False, iters=20,
+             dtype=torch.bfloat16, blocksparse=None, nbytes=None):
+        c = make_decode_case(dev, lens, Hq, Hkv, D, B, kvd, dtype=dtype)
         for ver in versions:
-            ms = time_device(attention_call(ops, c, ver), iters, flush=flush if small else None)
-            rec(f"{name} {ver}", workload, c["nbytes"], ms, kernel=ops.last_attention_path(),
-                tokens_per_s=round(len(lens) / ms * 1e3, 1))
+            ms = time_device(attention_call(ops, c, ver, blocksparse), iters, flush=flush if small else None)
+            rec(f"{name} {ver}", workload, nbytes if nbytes is not None else c["nbytes"], ms,
+                kernel=ops.last_attention_path(), tokens_per_s=round(len(lens) / ms * 1e3, 1))
         return c
 
     # config 1 (the reference's CPU-runnable case): v1 + reshape_and_cache, MHA 32 heads, 16 x 1024
@@ -497,6 +503,25 @@ def configs_extra(ops, dev, peak):
         rec(f"config4 reshape_and_cache fp8 T={T}", f"{T} tokens x 8 kv heads x 128, bf16 -> e4m3 (kv_scale 0.5)",
             T * 8 * 128 * 2 * (2 + 1), ms)
     del c4
+    torch.cuda.empty_cache()
+    # the general (SIMT) kernel family: what the TMA + mma.sync family does not instantiate (fp32 queries, block size 8,
+    # block-sparse masks) — coverage kernels, measured so that their distance from the roofline is on record
+    S_, L_ = 128, 4096
+    attn("simt fp32", "fp32 queries + fp32 cache (x = 4), 32q/8kv, head 128, block 16, 128 x 4096 ctx", [L_] * S_, 32, 8,
+         128, 16, dtype=torch.float32, iters=10)
+    torch.cuda.empty_cache()
+    attn("simt block8", "block size 8, bf16, 32q/8kv, head 128, 128 x 4096 ctx", [L_] * S_, 32, 8, 128, 8, iters=10)
+    torch.cuda.empty_cache()
+    # block-sparse (attention_kernels.cu:212-256): with head_sliding_step 0 a 64-token block k is read when
+    # k > q_block - local_blocks or (k + 1) % vert_stride == 0; only those blocks are algorithmic bytes
+    local_blocks, vert_stride, bs_block = 16, 8, 64
+    nb_ = L_ // bs_block
+    q_blk = (L_ - 1) // bs_block
+    visible = sum(1 for k in range(nb_) if k > q_blk - local_blocks or (k + 1) % vert_stride == 0)
+    attn("simt blocksparse", f"block-sparse (local {local_blocks} x {bs_block}-token blocks + every {vert_stride}th), "
+         f"bf16, 32q/8kv, head 128, block 16, 128 x 4096 ctx: {visible} of {nb_} blocks visible", [L_] * S_, 32, 8, 128,
+         16, iters=10, blocksparse=(local_blocks, vert_stride, bs_block, 0),
+         nbytes=algorithmic_bytes(S_, visible * bs_block, 32, 8, 128))
     torch.cuda.empty_cache()
     # config 5: ragged 128..128k mix, block 16 / 32, + copy_blocks / swap_blocks for prefix / beam sharing
     lens = ragged_lens()

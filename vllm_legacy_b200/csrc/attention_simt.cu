@@ -13,13 +13,33 @@
 
 namespace b200pa {
 
+// Element j (a compile-time constant after unrolling) of a 16-byte group, without a union (a union of an int4 and a
+// byte / float array is spilled to local memory by the compiler).
+__device__ __forceinline__ int word_of(const int4& v, int i) { return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w; }
+template <typename CT>
+__device__ __forceinline__ CT elem_of(const int4& v, int j);
+template <>
+__device__ __forceinline__ float elem_of<float>(const int4& v, int j) { return __int_as_float(word_of(v, j)); }
+template <>
+__device__ __forceinline__ __half elem_of<__half>(const int4& v, int j) {
+  return __ushort_as_half((unsigned short)((unsigned)word_of(v, j >> 1) >> (16 * (j & 1))));
+}
+template <>
+__device__ __forceinline__ __nv_bfloat16 elem_of<__nv_bfloat16>(const int4& v, int j) {
+  return __ushort_as_bfloat16((unsigned short)((unsigned)word_of(v, j >> 1) >> (16 * (j & 1))));
+}
+template <>
+__device__ __forceinline__ uint8_t elem_of<uint8_t>(const int4& v, int j) {
+  return (uint8_t)((unsigned)word_of(v, j >> 2) >> (8 * (j & 3)));
+}
+
 constexpr int kSimtWarps = 4;
 constexpr int kSimtThreads = kSimtWarps * 32;
 constexpr int kMaxHeadSize = 256;
 constexpr int kAccPerLane = kMaxHeadSize / 32;
 
 template <typename T, int KV, bool BLOCK_SPARSE>
-__global__ void __launch_bounds__(kSimtThreads)
+__global__ void __launch_bounds__(kSimtThreads, 5)  // <= 102 registers: 5 CTAs (20 warps) per SM, no spills (6 CTAs spill)
     paged_attention_simt_kernel(const __grid_constant__ AttnKernelParams p) {
   using CT = typename CacheElem<T, KV>::type;
   constexpr int X = 16 / sizeof(CT);
@@ -39,8 +59,8 @@ __global__ void __launch_bounds__(kSimtThreads)
   const float alibi = p.alibi_slopes ? p.alibi_slopes[head] : 0.f;
   const int* block_table = p.block_tables + (int64_t)seq * p.max_blocks_per_seq;
 
-  __shared__ float q_s[kMaxHeadSize];
-  __shared__ float p_s[kSimtWarps][32];
+  __shared__ __align__(16) float q_s[kMaxHeadSize];
+  __shared__ __align__(16) float p_s[kSimtWarps][32];
   __shared__ float red_m[kSimtWarps], red_l[kSimtWarps];
   __shared__ float red_acc[kSimtWarps][kMaxHeadSize];
 
@@ -64,17 +84,35 @@ __global__ void __launch_bounds__(kSimtThreads)
     bool valid = tok < t_end;
     if constexpr (BLOCK_SPARSE) valid = valid && bs.attended(tok / B, B);
     float logit = -FLT_MAX;
+    int64_t my_phys = 0;  // physical block of this lane's token (the P.V phase takes it by shuffle)
     if (valid) {
-      const int64_t phys = block_table[tok / B];
-      const CT* kp = kc + phys * p.kv_block_stride + (tok % B) * X;
-      float dot = 0.f;
-      for (int dh = 0; dh < D / X; ++dh) {
-        union { int4 v; CT e[X]; } kv;
-        kv.v = *reinterpret_cast<const int4*>(kp + (int64_t)dh * B * X);
+      my_phys = block_table[tok / B];
+      const CT* kp = kc + my_phys * p.kv_block_stride + (tok % B) * X;
+      // 16-byte K groups, four loads in flight before their products; q comes from shared memory as float4
+      // (broadcast), and the products go to two accumulators by turns so that the FMA chain is half as long
+      float dot0 = 0.f, dot1 = 0.f;
+      const int ndh = D / X;
+      for (int dh0 = 0; dh0 < ndh; dh0 += 4) {
+        int4 kv[4];
 #pragma unroll
-        for (int j = 0; j < X; ++j) dot = fmaf(q_s[dh * X + j], CacheElem<T, KV>::load(&kv.e[j], p.kv_scale), dot);
+        for (int i = 0; i < 4; ++i)
+          if (dh0 + i < ndh) kv[i] = *reinterpret_cast<const int4*>(kp + (int64_t)(dh0 + i) * B * X);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          if (dh0 + i < ndh) {
+            const float4* q4 = reinterpret_cast<const float4*>(q_s + (dh0 + i) * X);
+#pragma unroll
+            for (int j4 = 0; j4 < X / 4; ++j4) {
+              const float4 qv = q4[j4];
+              dot0 = fmaf(qv.x, CacheElem<T, KV>::val(elem_of<CT>(kv[i], 4 * j4 + 0), p.kv_scale), dot0);
+              dot1 = fmaf(qv.y, CacheElem<T, KV>::val(elem_of<CT>(kv[i], 4 * j4 + 1), p.kv_scale), dot1);
+              dot0 = fmaf(qv.z, CacheElem<T, KV>::val(elem_of<CT>(kv[i], 4 * j4 + 2), p.kv_scale), dot0);
+              dot1 = fmaf(qv.w, CacheElem<T, KV>::val(elem_of<CT>(kv[i], 4 * j4 + 3), p.kv_scale), dot1);
+            }
+          }
+        }
       }
-      logit = dot * p.scale + alibi * (float)(tok - seq_len + 1);
+      logit = (dot0 + dot1) * p.scale + alibi * (float)(tok - seq_len + 1);
     }
     const float m_new = fmaxf(m, warp_max(logit));
     const float alpha = __expf(m - m_new);
@@ -92,18 +130,67 @@ __global__ void __launch_bounds__(kSimtThreads)
       if constexpr (BLOCK_SPARSE) {
         if (!bs.attended(blk, B)) continue;
       }
-      const int64_t phys = block_table[blk];
-      const int n_here = min(B, t_stop - tb);  // never touches tokens >= seq_len (stale cache bits)
+      // the block's first token belongs to lane tb - t0, which is valid (and attended) here
+      const int64_t phys = __shfl_sync(0xffffffffu, my_phys, tb - t0);
+      const int n_here = min(B, t_stop - tb);  // never uses tokens >= seq_len (stale cache bits)
       const CT* vb = vc + phys * p.kv_block_stride;
       const float* pp = &p_s[warp][tb - t0];
+      if (B % X == 0) {
+        // a row's B tokens are whole 16-byte groups: one 128-bit load per (row, group), all of the lane's rows in
+        // flight before their products; p as float4 (tb - t0 is a multiple of B).  Tokens >= n_here are loaded (the
+        // bytes exist) but never used.
+        for (int j0 = 0; j0 < n_here; j0 += X) {
+          int4 rv[kAccPerLane];
 #pragma unroll
-      for (int k = 0; k < kAccPerLane; ++k) {
-        const int d = lane + 32 * k;
-        if (d < D) {
-          const CT* row = vb + (int64_t)d * B;
-          float a = acc[k];
-          for (int j = 0; j < n_here; ++j) a = fmaf(pp[j], CacheElem<T, KV>::load(row + j, p.kv_scale), a);
-          acc[k] = a;
+          for (int k = 0; k < kAccPerLane; ++k)
+            if (lane + 32 * k < D) rv[k] = *reinterpret_cast<const int4*>(vb + (int64_t)(lane + 32 * k) * B + j0);
+          float4 pv[X / 4];
+#pragma unroll
+          for (int j4 = 0; j4 < X / 4; ++j4) pv[j4] = *reinterpret_cast<const float4*>(pp + j0 + 4 * j4);
+          const int left = n_here - j0;
+          if (left >= X) {
+#pragma unroll
+            for (int k = 0; k < kAccPerLane; ++k) {
+              if (lane + 32 * k < D) {
+                float a = acc[k];
+#pragma unroll
+                for (int j4 = 0; j4 < X / 4; ++j4) {
+                  a = fmaf(pv[j4].x, CacheElem<T, KV>::val(elem_of<CT>(rv[k], 4 * j4 + 0), p.kv_scale), a);
+                  a = fmaf(pv[j4].y, CacheElem<T, KV>::val(elem_of<CT>(rv[k], 4 * j4 + 1), p.kv_scale), a);
+                  a = fmaf(pv[j4].z, CacheElem<T, KV>::val(elem_of<CT>(rv[k], 4 * j4 + 2), p.kv_scale), a);
+                  a = fmaf(pv[j4].w, CacheElem<T, KV>::val(elem_of<CT>(rv[k], 4 * j4 + 3), p.kv_scale), a);
+                }
+                acc[k] = a;
+              }
+            }
+          } else {  // the sequence ends inside this group
+#pragma unroll
+            for (int k = 0; k < kAccPerLane; ++k) {
+              if (lane + 32 * k < D) {
+                float a = acc[k];
+#pragma unroll
+                for (int j4 = 0; j4 < X / 4; ++j4) {
+                  const int l4 = left - 4 * j4;
+                  if (l4 > 0) a = fmaf(pv[j4].x, CacheElem<T, KV>::val(elem_of<CT>(rv[k], 4 * j4 + 0), p.kv_scale), a);
+                  if (l4 > 1) a = fmaf(pv[j4].y, CacheElem<T, KV>::val(elem_of<CT>(rv[k], 4 * j4 + 1), p.kv_scale), a);
+                  if (l4 > 2) a = fmaf(pv[j4].z, CacheElem<T, KV>::val(elem_of<CT>(rv[k], 4 * j4 + 2), p.kv_scale), a);
+                  if (l4 > 3) a = fmaf(pv[j4].w, CacheElem<T, KV>::val(elem_of<CT>(rv[k], 4 * j4 + 3), p.kv_scale), a);
+                }
+                acc[k] = a;
+              }
+            }
+          }
+        }
+      } else {  // rows shorter than 16 bytes (fp8 cache with block size 8): element loads
+#pragma unroll
+        for (int k = 0; k < kAccPerLane; ++k) {
+          const int d = lane + 32 * k;
+          if (d < D) {
+            const CT* row = vb + (int64_t)d * B;
+            float a = acc[k];
+            for (int j = 0; j < n_here; ++j) a = fmaf(pp[j], CacheElem<T, KV>::load(row + j, p.kv_scale), a);
+            acc[k] = a;
+          }
         }
       }
     }

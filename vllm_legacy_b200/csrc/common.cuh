@@ -82,11 +82,13 @@ struct CacheElem {
     // value the reference kernel would see after scaled_convert<T, uint8_t>
     return to_float<T>(fp8_dequant<KV, T>(*p, scale));
   }
+  static __device__ __forceinline__ float val(uint8_t b, float scale) { return to_float<T>(fp8_dequant<KV, T>(b, scale)); }
 };
 template <typename T>
 struct CacheElem<T, B200PA_KV_AUTO> {
   using type = T;
   static __device__ __forceinline__ float load(const T* p, float) { return to_float<T>(*p); }
+  static __device__ __forceinline__ float val(T v, float) { return to_float<T>(v); }
 };
 
 // Store side: element written to the cache for a source element of type T (KV == AUTO: unchanged).
