@@ -14,9 +14,9 @@ from tests import helpers  # noqa: E402
 from vllm_legacy_b200 import _custom_ops as ops  # noqa: E402
 
 
-def ref_v2_call(ref, out, es, ml, tmp, q, kc, vc, nkv, scale, bt, sl, B, maxlen, alibi, kvd, kvs):
+def ref_v2_call(ref, out, es, ml, tmp, q, kc, vc, nkv, scale, bt, sl, B, maxlen, alibi, kvd, kvs, bs=(0, 0, 64, 0)):
     ref.paged_attention_v2(out, es, ml, tmp, q, str(kc.data_ptr()), kc.stride(0), kc.stride(1),
-                           str(vc.data_ptr()), nkv, scale, bt, sl, B, maxlen, alibi, kvd, kvs, 0, 0, 0, 64, 0)
+                           str(vc.data_ptr()), nkv, scale, bt, sl, B, maxlen, alibi, kvd, kvs, 0, *bs)
 
 
 def attention_case(ref, S, Hq, Hkv, D, B, dtype, kvd, maxlen, alibi=False, seed=0, version="v2", kv_scale=1.0):
@@ -88,12 +88,14 @@ def timed(fn, iters=10, warmup=3, flush=None):
     return ts[len(ts) // 2]
 
 
-def timing_case(ref, S, Hq, Hkv, D, B, dtype, kvd, L, label):
+def timing_case(ref, S, Hq, Hkv, D, B, dtype, kvd, L, label, bs=None, visible_frac=1.0):
+    """bs = (local_blocks, vert_stride, block_size, head_sliding_step) runs the block-sparse kernels (v2 only);
+    visible_frac scales the algorithmic bytes to the blocks the mask lets through."""
     dev = "cuda"
     scale = D ** -0.5
     nblk = (L + B - 1) // B
     NB = S * nblk + 16
-    esz = 1 if kvd == "fp8" else 2
+    esz = 1 if kvd == "fp8" else torch.empty(0, dtype=dtype).element_size()
     x = 16 // esz
     cdt = torch.uint8 if kvd == "fp8" else dtype
     kc = torch.empty(NB, Hkv, D // x, B, x, dtype=cdt, device=dev)
@@ -112,21 +114,22 @@ def timing_case(ref, S, Hq, Hkv, D, B, dtype, kvd, L, label):
     es = torch.empty(S, Hq, P, dtype=torch.float32, device=dev)
     ml = torch.empty_like(es)
     tmp = torch.empty(S, Hq, P, D, dtype=dtype, device=dev)
-    nbytes = S * L * Hkv * D * 2 * esz + 2 * S * Hq * D * 2
+    nbytes = int(S * L * visible_frac) * Hkv * D * 2 * esz + 2 * S * Hq * D * q.element_size()
     rows = []
-    f1 = lambda: ops.paged_attention_v1(out, q, kc, vc, Hkv, scale, bt, sl, B, L, None, kvd, 1.0)
-    f2 = lambda: ops.paged_attention_v2(out, es, ml, tmp, q, kc, vc, Hkv, scale, bt, sl, B, L, None, kvd, 1.0)
+    bsa = bs if bs is not None else (0, 0, 64, 0)
+    f1 = lambda: ops.paged_attention_v1(out, q, kc, vc, Hkv, scale, bt, sl, B, L, None, kvd, 1.0, 0, *bsa)
+    f2 = lambda: ops.paged_attention_v2(out, es, ml, tmp, q, kc, vc, Hkv, scale, bt, sl, B, L, None, kvd, 1.0, 0, *bsa)
     for name, fn in (("ours v1", f1), ("ours v2", f2)):
         ms = timed(fn)
         rows.append((name, ms, ops.last_attention_path(), ops.last_attention_partitions()))
     if ref is not None:
-        if L <= 8192 * 4:
+        if L <= 8192 * 4 and bs is None:
             try:
                 g1 = lambda: ref.paged_attention_v1(out, q, kc, vc, Hkv, scale, bt, sl, B, L, None, kvd, 1.0, 0, 0, 0, 64, 0)
                 rows.append(("ref  v1", timed(g1, iters=5, warmup=2), "ref", 1))
             except Exception as e:  # noqa: BLE001
                 print("ref v1 failed:", e)
-        g2 = lambda: ref_v2_call(ref, out, es, ml, tmp, q, kc, vc, Hkv, scale, bt, sl, B, L, None, kvd, 1.0)
+        g2 = lambda: ref_v2_call(ref, out, es, ml, tmp, q, kc, vc, Hkv, scale, bt, sl, B, L, None, kvd, 1.0, bsa)
         rows.append(("ref  v2", timed(g2, iters=5, warmup=2), "ref", P))
     for name, ms, path, parts in rows:
         print(f"[{label}] {name}: {ms:8.3f} ms  {nbytes / ms / 1e6:8.1f} GB/s  ({nbytes / ms / 1e6 / 6553 * 100:5.1f}% of 6553)  "
@@ -168,6 +171,13 @@ def main():
         timing_case(ref, 256, 32, 8, 128, 16, bf, "auto", 4096, "C2 256x4096 gqa4")
         timing_case(ref, 256, 8, 1, 128, 16, bf, "auto", 8192, "C3/tp8 256x8192 g8")
         timing_case(ref, 128, 32, 8, 128, 16, bf, "fp8", 32768, "C4 128x32k fp8")
+        # the general (SIMT) family: fp32, block size 8, block-sparse (bench.py extra.configs "simt ...")
+        timing_case(ref, 128, 32, 8, 128, 16, f32, "auto", 4096, "SIMT fp32 128x4096")
+        timing_case(ref, 128, 32, 8, 128, 8, bf, "auto", 4096, "SIMT block8 128x4096")
+        nb, qb = 4096 // 64, (4096 - 1) // 64
+        vis = sum(1 for k in range(nb) if k > qb - 16 or (k + 1) % 8 == 0)
+        timing_case(ref, 128, 32, 8, 128, 16, bf, "auto", 4096, "SIMT blocksparse 128x4096", bs=(16, 8, 64, 0),
+                    visible_frac=vis / nb)
 
 
 if __name__ == "__main__":

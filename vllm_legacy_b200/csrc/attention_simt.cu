@@ -8,6 +8,7 @@
 // per warp (no full-sequence logits in shared memory, so no max_seq_len limit for v1), lanes
 // mapped to consecutive tokens for K (16-byte loads) and to consecutive head-dim rows for V.
 #include <cfloat>
+#include <type_traits>
 
 #include "attention_common.cuh"
 
@@ -31,6 +32,22 @@ __device__ __forceinline__ __nv_bfloat16 elem_of<__nv_bfloat16>(const int4& v, i
 template <>
 __device__ __forceinline__ uint8_t elem_of<uint8_t>(const int4& v, int j) {
   return (uint8_t)((unsigned)word_of(v, j >> 2) >> (8 * (j & 3)));
+}
+
+// Elements j, j + 1 (j even, a compile-time constant after unrolling) of a 16-byte group as floats, i.e. the value the
+// reference kernel sees after its load-time conversion.  16-bit caches convert the packed pair straight from its word
+// (bf16: one shift / one mask; fp16: one packed convert) instead of extracting and converting element by element.
+template <typename T, int KV, typename CT>
+__device__ __forceinline__ float2 pair_of(const int4& v, int j, float kv_scale) {
+  if constexpr (KV == B200PA_KV_AUTO && std::is_same<CT, __nv_bfloat16>::value) {
+    const unsigned w = (unsigned)word_of(v, j >> 1);
+    return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+  } else if constexpr (KV == B200PA_KV_AUTO && std::is_same<CT, __half>::value) {
+    const unsigned w = (unsigned)word_of(v, j >> 1);
+    return __half22float2(*reinterpret_cast<const __half2*>(&w));
+  } else {
+    return make_float2(CacheElem<T, KV>::val(elem_of<CT>(v, j), kv_scale), CacheElem<T, KV>::val(elem_of<CT>(v, j + 1), kv_scale));
+  }
 }
 
 constexpr int kSimtWarps = 4;
@@ -104,10 +121,12 @@ __global__ void __launch_bounds__(kSimtThreads, 5)  // <= 102 registers: 5 CTAs 
 #pragma unroll
             for (int j4 = 0; j4 < X / 4; ++j4) {
               const float4 qv = q4[j4];
-              dot0 = fmaf(qv.x, CacheElem<T, KV>::val(elem_of<CT>(kv[i], 4 * j4 + 0), p.kv_scale), dot0);
-              dot1 = fmaf(qv.y, CacheElem<T, KV>::val(elem_of<CT>(kv[i], 4 * j4 + 1), p.kv_scale), dot1);
-              dot0 = fmaf(qv.z, CacheElem<T, KV>::val(elem_of<CT>(kv[i], 4 * j4 + 2), p.kv_scale), dot0);
-              dot1 = fmaf(qv.w, CacheElem<T, KV>::val(elem_of<CT>(kv[i], 4 * j4 + 3), p.kv_scale), dot1);
+              const float2 k01 = pair_of<T, KV, CT>(kv[i], 4 * j4, p.kv_scale);
+              const float2 k23 = pair_of<T, KV, CT>(kv[i], 4 * j4 + 2, p.kv_scale);
+              dot0 = fmaf(qv.x, k01.x, dot0);
+              dot1 = fmaf(qv.y, k01.y, dot1);
+              dot0 = fmaf(qv.z, k23.x, dot0);
+              dot1 = fmaf(qv.w, k23.y, dot1);
             }
           }
         }
@@ -155,10 +174,12 @@ __global__ void __launch_bounds__(kSimtThreads, 5)  // <= 102 registers: 5 CTAs 
                 float a = acc[k];
 #pragma unroll
                 for (int j4 = 0; j4 < X / 4; ++j4) {
-                  a = fmaf(pv[j4].x, CacheElem<T, KV>::val(elem_of<CT>(rv[k], 4 * j4 + 0), p.kv_scale), a);
-                  a = fmaf(pv[j4].y, CacheElem<T, KV>::val(elem_of<CT>(rv[k], 4 * j4 + 1), p.kv_scale), a);
-                  a = fmaf(pv[j4].z, CacheElem<T, KV>::val(elem_of<CT>(rv[k], 4 * j4 + 2), p.kv_scale), a);
-                  a = fmaf(pv[j4].w, CacheElem<T, KV>::val(elem_of<CT>(rv[k], 4 * j4 + 3), p.kv_scale), a);
+                  const float2 v01 = pair_of<T, KV, CT>(rv[k], 4 * j4, p.kv_scale);
+                  const float2 v23 = pair_of<T, KV, CT>(rv[k], 4 * j4 + 2, p.kv_scale);
+                  a = fmaf(pv[j4].x, v01.x, a);
+                  a = fmaf(pv[j4].y, v01.y, a);
+                  a = fmaf(pv[j4].z, v23.x, a);
+                  a = fmaf(pv[j4].w, v23.y, a);
                 }
                 acc[k] = a;
               }
