@@ -504,8 +504,9 @@ def configs_extra(ops, dev, peak):
             T * 8 * 128 * 2 * (2 + 1), ms)
     del c4
     torch.cuda.empty_cache()
-    # the general (SIMT) kernel family: what the TMA + mma.sync family does not instantiate (fp32 queries, block size 8,
-    # block-sparse masks) — coverage kernels, measured so that their distance from the roofline is on record
+    # the general (SIMT) kernel family: what the TMA + mma.sync family does not instantiate (fp32 queries, block size 8)
+    # — coverage kernels, measured so that their distance from the roofline is on record — and block-sparse masks,
+    # which 16-bit queries with head size 64 / 128 run on the mma family (filtered block iterator)
     S_, L_ = 128, 4096
     attn("simt fp32", "fp32 queries + fp32 cache (x = 4), 32q/8kv, head 128, block 16, 128 x 4096 ctx", [L_] * S_, 32, 8,
          128, 16, dtype=torch.float32, iters=10)
@@ -518,7 +519,7 @@ def configs_extra(ops, dev, peak):
     nb_ = L_ // bs_block
     q_blk = (L_ - 1) // bs_block
     visible = sum(1 for k in range(nb_) if k > q_blk - local_blocks or (k + 1) % vert_stride == 0)
-    attn("simt blocksparse", f"block-sparse (local {local_blocks} x {bs_block}-token blocks + every {vert_stride}th), "
+    attn("blocksparse", f"block-sparse (local {local_blocks} x {bs_block}-token blocks + every {vert_stride}th), "
          f"bf16, 32q/8kv, head 128, block 16, 128 x 4096 ctx: {visible} of {nb_} blocks visible", [L_] * S_, 32, 8, 128,
          16, iters=10, blocksparse=(local_blocks, vert_stride, bs_block, 0),
          nbytes=algorithmic_bytes(S_, visible * bs_block, 32, 8, 128))

@@ -179,7 +179,8 @@ def test_blocksparse_paged_attention(ops, oracle, version, head_sliding_step, nu
     out = torch.empty_like(q, device=DEV)
     _run(ops, version, out, q.to(DEV), kc.to(DEV), vc.to(DEV), Hkv, scale, bt.to(DEV), sl.to(DEV), block_size, max_len,
          None, kv_cache_dtype, 1.0, bs)
-    assert ops.last_attention_path() == "simt"
+    # 16-bit queries with head size 64 / 128 run the block-sparse variant of the TMA + mma.sync kernel, fp32 the SIMT one
+    assert ops.last_attention_path() == ("simt" if dtype == torch.float else "mma_tma")
     tol = 1e-3 if kv_cache_dtype == "auto" else 1e-2
     assert torch.allclose(out.cpu().float(), want.float(), atol=tol, rtol=1e-2)
     # and it really differs from dense attention
@@ -187,6 +188,50 @@ def test_blocksparse_paged_attention(ops, oracle, version, head_sliding_step, nu
     _run(ops, version, dense, q.to(DEV), kc.to(DEV), vc.to(DEV), Hkv, scale, bt.to(DEV), sl.to(DEV), block_size,
          max_len, None, kv_cache_dtype, 1.0)
     assert (dense[2] - out[2]).abs().max() > 1e-4
+
+
+@pytest.mark.parametrize("version", ["v1", "v2"])
+@pytest.mark.parametrize("heads", [(8, 2), (32, 4), (32, 2), (24, 1), (6, 6)])   # groups 4, 8, 16, 24 (2 q-tiles), 1
+@pytest.mark.parametrize("head_size", [64, 128])
+@pytest.mark.parametrize("sparse", [(2, 4, 32, 1), (16, 8, 64, 0), (1, 16, 64, 3), (4, 2, 128, -2), (3, 5, 64, 2)])
+@pytest.mark.parametrize("block_size,kv_cache_dtype,alibi", [(16, "auto", False), (32, "auto", True), (16, "fp8", False),
+                                                             (32, "fp8_e5m2", False)])
+@torch.inference_mode()
+def test_blocksparse_mma_family(ops, oracle, version, heads, head_size, sparse, block_size, kv_cache_dtype, alibi):
+    """The block-sparse variant of the TMA + mma.sync kernel (filtered block iterator shared by consumer and TMA
+    producer, per-row masks where the heads' offsets differ) vs the oracle: (local_blocks, vert_stride, sparse block,
+    head_sliding_step) incl. per-head and per-KV-head offsets, GQA groups up to 24, contexts long enough to split,
+    lengths ending inside a block / a sparse block, ALiBi, fp8."""
+    torch.manual_seed(7)
+    Hq, Hkv = heads
+    D, NB = head_size, 640
+    lens = [1, 63, 64, 700, 4100, 9001]
+    S, max_len = len(lens), max(lens)
+    scale = float(D ** -0.5)
+    dtype = torch.bfloat16 if kv_cache_dtype != "fp8" else torch.half
+    q = torch.empty(S, Hq, D, dtype=dtype).uniform_(-scale, scale)
+    # (the helper builds e4m3 bytes; read as e5m2 they are other, still finite, values — fine for a parity test)
+    kcs, vcs = helpers.create_kv_caches_with_random(NB, block_size, 1, Hkv, D,
+                                                    "fp8" if kv_cache_dtype != "auto" else "auto", dtype, 3, "cpu",
+                                                    oracle.convert_fp8)
+    kc, vc = kcs[0], vcs[0]
+    nblk = (max_len + block_size - 1) // block_size
+    bt = torch.tensor(helpers.make_block_tables(S, nblk, NB, 3), dtype=torch.int32)
+    sl = torch.tensor(lens, dtype=torch.int32)
+    al = torch.randn(Hq, dtype=torch.float32) * 0.1 if alibi else None
+    kv_scale = 1.0 if kv_cache_dtype == "auto" else 0.5
+    want = torch.empty_like(q)
+    oracle.paged_attention_v1(want, q, kc, vc, Hkv, scale, bt, sl, block_size, max_len, al, kv_cache_dtype, kv_scale, 0,
+                              *sparse)
+    out = torch.full_like(q, float("nan"), device=DEV)
+    _run(ops, version, out, q.to(DEV), kc.to(DEV), vc.to(DEV), Hkv, scale, bt.to(DEV), sl.to(DEV), block_size, max_len,
+         al.to(DEV) if al is not None else None, kv_cache_dtype, kv_scale, sparse)
+    assert ops.last_attention_path() == "mma_tma"
+    assert not torch.isnan(out).any()
+    tol = 1e-3 if kv_cache_dtype == "auto" else 1e-2
+    ref_mag = want.float().abs().max().item() + 1e-6
+    assert torch.allclose(out.cpu().float(), want.float(), atol=max(tol, tol * ref_mag), rtol=1e-2), \
+        (out.cpu().float() - want.float()).abs().max()
 
 
 @pytest.mark.parametrize("case", ["attn_bf16_gqa", "attn_f32_alibi", "attn_bf16_long"])

@@ -13,7 +13,7 @@ namespace b200pa {
 constexpr int kSmemPerSM = 227 * 1024;       // usable shared memory per SM / max per CTA (opt-in)
 constexpr int kSmemReservedPerCta = 1024;    // system-reserved shared memory per resident CTA
 
-template <typename T, int KV, int D, int B, int NG>
+template <typename T, int KV, int D, int B, int NG, bool BS = false>
 static int launch_one(AttnKernelParams kp, int num_seqs, cudaStream_t stream) {
   constexpr int CTB = KV == B200PA_KV_AUTO ? 2 : 1;
   constexpr int STAGE = 2 * B * D * CTB;
@@ -47,7 +47,7 @@ static int launch_one(AttnKernelParams kp, int num_seqs, cudaStream_t stream) {
   }
   kp.num_stages = nst;
   const int smem = total_bytes(nst);
-  auto kernel = paged_attention_mma_kernel<T, KV, D, B, NG>;
+  auto kernel = paged_attention_mma_kernel<T, KV, D, B, NG, BS>;
   // cudaFuncSetAttribute is per device; remember the largest value configured on each.
   static int configured[64] = {0};
   int dev = 0;
@@ -67,6 +67,19 @@ static int launch_one(AttnKernelParams kp, int num_seqs, cudaStream_t stream) {
 template <typename T, int KV, int D>
 static int launch_bg(const AttnKernelParams& kp, int num_seqs, cudaStream_t stream) {
   const int G = kp.num_heads / kp.num_kv_heads;
+  if (kp.bs_vert_stride > 1) {
+    // block-sparse masks: instantiated for the head sizes the block-sparse models use (phi-3-small: 128); the general
+    // (SIMT) family takes the rest
+    if constexpr (D == 64 || D == 128) {
+      if (kp.block_size == 16)
+        return G <= 8 ? launch_one<T, KV, D, 16, 1, true>(kp, num_seqs, stream)
+                      : launch_one<T, KV, D, 16, 2, true>(kp, num_seqs, stream);
+      if (kp.block_size == 32)
+        return G <= 8 ? launch_one<T, KV, D, 32, 1, true>(kp, num_seqs, stream)
+                      : launch_one<T, KV, D, 32, 2, true>(kp, num_seqs, stream);
+    }
+    return 1;
+  }
   if (kp.block_size == 16)
     return G <= 8 ? launch_one<T, KV, D, 16, 1>(kp, num_seqs, stream) : launch_one<T, KV, D, 16, 2>(kp, num_seqs, stream);
   if (kp.block_size == 32)

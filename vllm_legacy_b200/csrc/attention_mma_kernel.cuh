@@ -310,7 +310,11 @@ __device__ __forceinline__ void decode_epilogue(const AttnKernelParams& p, uint8
 
 // T: query/out type (half | bf16).  KV: b200pa_kv_dtype_t.  D: head size.  B: block size (16|32).
 // NG: 8-row query-head tiles per CTA (1: group <= 8, 2: group <= 16 per CTA).
-template <typename T, int KV, int D, int B, int NG>
+// BS: block-sparse masks (attention_kernels.cu:212-256, 387-393).  A warp then walks only the KV blocks that at least
+// one head of the CTA's group attends: consumer and TMA producer step through the same filtered sequence (`nxt`), the
+// ring's stage / phase count attended blocks, and where the heads' offsets differ (head_sliding_step != 0) a row that
+// does not attend a block gets p = 0 for it.  The dense instantiations (BS = false) compile to the same code as before.
+template <typename T, int KV, int D, int B, int NG, bool BS = false>
 __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
     paged_attention_mma_kernel(const __grid_constant__ AttnKernelParams p) {
   using MT = typename std::conditional<KV == B200PA_KV_AUTO, T, __half>::type;  // tensor-core input type
@@ -375,24 +379,65 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
   const char* vbase = static_cast<const char*>(p.v_cache) + (int64_t)kv_head * p.kv_head_stride * CTB;
   const int64_t blk_stride_bytes = p.kv_block_stride * CTB;
 
+  // ---- block-sparse: which of this warp's blocks does any head of the group attend? ---------------
+  BlockSparse bs_lane;     // lane l < HPT: head l of the CTA's q-tile (the any-head test is a warp vote)
+  BlockSparse bs_row[NG];  // the heads of this lane's S-fragment rows
+  bool lane_head = false;
+  if constexpr (BS) {
+    const int hl = qt * HPT + lane;
+    lane_head = lane < HPT && hl < G;
+    bs_lane.init(p, seq_len, kv_head * G + (lane_head ? hl : 0), kv_head);
+#pragma unroll
+    for (int r = 0; r < NG; ++r) bs_row[r].init(p, seq_len, kv_head * G + min(qt * HPT + gid + 8 * r, G - 1), kv_head);
+  }
+  // first ordinal >= i of this warp's blocks that is attended (warp-uniform; identity when dense)
+  auto nxt = [&](int i) -> int {
+    if constexpr (BS) {
+      while (i < my_n) {
+        const bool a = lane_head && bs_lane.attended(blk_begin + warp + i * kMmaWarps, B);
+        if (__any_sync(0xffffffffu, a)) break;
+        ++i;
+      }
+    }
+    return i;
+  };
+
   // ---- pipeline prologue: barriers + first NST blocks in flight --------------------------------
   uint64_t policy = 0;
   int next_phys = 0;
+  int pi = 0;  // block-sparse: the producer's cursor into the filtered sequence (warp-uniform)
   if (lane == 0) {
     for (int s = 0; s < NST; ++s) mbar_init(bar_base + s * 8, 1);
     fence_proxy_async_smem();
     policy = (p.flags & 1) ? l2_evict_normal_policy() : l2_evict_first_policy();
-    const int n0 = min(NST, my_n);
-    for (int i = 0; i < n0; ++i) {
-      const int64_t phys = block_table[i * kMmaWarps];
-      const uint32_t bar = bar_base + i * 8, dst = stage_base + i * STAGE;
-      mbar_arrive_expect_tx(bar, STAGE);
-      tma_bulk_g2s(dst, kbase + phys * blk_stride_bytes, CHUNK, bar, policy);
-      tma_bulk_g2s(dst + CHUNK, vbase + phys * blk_stride_bytes, CHUNK, bar, policy);
+    if constexpr (!BS) {
+      const int n0 = min(NST, my_n);
+      for (int i = 0; i < n0; ++i) {
+        const int64_t phys = block_table[i * kMmaWarps];
+        const uint32_t bar = bar_base + i * 8, dst = stage_base + i * STAGE;
+        mbar_arrive_expect_tx(bar, STAGE);
+        tma_bulk_g2s(dst, kbase + phys * blk_stride_bytes, CHUNK, bar, policy);
+        tma_bulk_g2s(dst + CHUNK, vbase + phys * blk_stride_bytes, CHUNK, bar, policy);
+      }
+      if (NST < my_n) next_phys = block_table[NST * kMmaWarps];
     }
-    if (NST < my_n) next_phys = block_table[NST * kMmaWarps];
   }
   __syncwarp();
+  if constexpr (BS) {
+    for (int s = 0; s < NST; ++s) {
+      pi = nxt(pi);
+      if (pi >= my_n) break;
+      if (lane == 0) {
+        const int64_t phys = block_table[pi * kMmaWarps];
+        const uint32_t bar = bar_base + s * 8, dst = stage_base + s * STAGE;
+        mbar_arrive_expect_tx(bar, STAGE);
+        tma_bulk_g2s(dst, kbase + phys * blk_stride_bytes, CHUNK, bar, policy);
+        tma_bulk_g2s(dst + CHUNK, vbase + phys * blk_stride_bytes, CHUNK, bar, policy);
+      }
+      ++pi;
+    }
+    __syncwarp();
+  }
 
   // ---- Q fragments (A operand of QK^T), resident for the whole kernel --------------------------
   // 16-bit cache: k index of step ks <-> d = 16ks + {2tig, 2tig+1 | +8};
@@ -474,12 +519,18 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
 
   int stage = 0;
   uint32_t phase = 0;
-  for (int i = 0; i < my_n; ++i) {
+  for (int i = nxt(0); i < my_n; i = nxt(i + 1)) {
     const uint32_t bar = bar_base + stage * 8;
     const uint32_t kb = stage_base + stage * STAGE;
     const uint32_t vb = kb + CHUNK;
     const int blk_tok0 = (blk_begin + warp + i * kMmaWarps) * B;  // first token of this block
     const int n_valid = t_end - blk_tok0;                         // >= 1; < B only in the last block
+    bool att[NG];  // block-sparse: does the head of fragment row r attend this block?
+#pragma unroll
+    for (int r = 0; r < NG; ++r) {
+      att[r] = true;
+      if constexpr (BS) att[r] = bs_row[r].attended(blk_begin + warp + i * kMmaWarps, B);
+    }
     mbar_wait(bar, phase);
 
     // ================= S = Q K^T =================
@@ -559,6 +610,9 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
           const int tin = tpos[nt] + e;
           if (has_alibi) v = fmaf(alibi_l2[r], (float)(blk_tok0 + tin - seq_len + 1), v);
           if (tin >= n_valid) v = kNegBig;
+          if constexpr (BS) {
+            if (!att[r]) v = kNegBig;  // (the running max must not move for a row that skips this block)
+          }
           z[nt][e] = v;
           mx = fmaxf(mx, v);
         }
@@ -571,7 +625,10 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
       float sum = 0.f;
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt) {
-        const float p0 = fast_exp2(z[nt][0] - m_new), p1 = fast_exp2(z[nt][1] - m_new);
+        float p0 = fast_exp2(z[nt][0] - m_new), p1 = fast_exp2(z[nt][1] - m_new);
+        if constexpr (BS) {
+          if (!att[r]) p0 = p1 = 0.f;  // exp2(-big - (-big)) would be 1 while the row has seen no token yet
+        }
         sum += p0 + p1;
         pk[r][nt] = pack2<MT>(p0, p1);
       }
@@ -662,7 +719,19 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
 
     // ================= refill this stage with block i + NST =================
     __syncwarp();
-    if (lane == 0 && i + NST < my_n) {
+    if constexpr (BS) {
+      pi = nxt(pi);  // the next attended block nobody has issued yet
+      if (pi < my_n) {
+        if (lane == 0) {
+          fence_proxy_async_smem();
+          const int64_t phys = block_table[pi * kMmaWarps];
+          mbar_arrive_expect_tx(bar, STAGE);
+          tma_bulk_g2s(kb, kbase + phys * blk_stride_bytes, CHUNK, bar, policy);
+          tma_bulk_g2s(vb, vbase + phys * blk_stride_bytes, CHUNK, bar, policy);
+        }
+        ++pi;
+      }
+    } else if (lane == 0 && i + NST < my_n) {
       fence_proxy_async_smem();
       const int64_t phys = next_phys;
       mbar_arrive_expect_tx(bar, STAGE);
