@@ -506,7 +506,7 @@ def configs_extra(ops, dev, peak):
     torch.cuda.empty_cache()
     # the general (SIMT) kernel family: what the TMA + mma.sync family does not instantiate (fp32 queries, block size 8)
     # — coverage kernels, measured so that their distance from the roofline is on record — and block-sparse masks,
-    # which 16-bit queries with head size 64 / 128 run on the mma family (filtered block iterator)
+    # which 16-bit queries with head size 64 / 112 / 128 run on the mma family (filtered block iterator)
     S_, L_ = 128, 4096
     attn("simt fp32", "fp32 queries + fp32 cache (x = 4), 32q/8kv, head 128, block 16, 128 x 4096 ctx", [L_] * S_, 32, 8,
          128, 16, dtype=torch.float32, iters=10)

@@ -81,6 +81,8 @@ def test_static_scratch_entry_point_validation(lib):
     assert f(ctypes.byref(_params(num_seqs=2048, num_heads=8, num_kv_heads=1, max_seq_len=4096, **fake, **strides)), None) == -8
     lib.b200pa_status_string.restype = ctypes.c_char_p
     assert b"static scratch" in lib.b200pa_status_string(-8)
+    # dense only: block-sparse parameters are an invalid argument here (b200pa_paged_attention_v1 / _v2 serve them)
+    assert f(ctypes.byref(_params(blocksparse_vert_stride=8, blocksparse_block_size=64, **fake, **strides)), None) == -5
 
 
 def test_attention_argument_validation(lib):

@@ -192,7 +192,7 @@ def test_blocksparse_paged_attention(ops, oracle, version, head_sliding_step, nu
 
 @pytest.mark.parametrize("version", ["v1", "v2"])
 @pytest.mark.parametrize("heads", [(8, 2), (32, 4), (32, 2), (24, 1), (6, 6)])   # groups 4, 8, 16, 24 (2 q-tiles), 1
-@pytest.mark.parametrize("head_size", [64, 128])
+@pytest.mark.parametrize("head_size", [64, 112, 128])
 @pytest.mark.parametrize("sparse", [(2, 4, 32, 1), (16, 8, 64, 0), (1, 16, 64, 3), (4, 2, 128, -2), (3, 5, 64, 2)])
 @pytest.mark.parametrize("block_size,kv_cache_dtype,alibi", [(16, "auto", False), (32, "auto", True), (16, "fp8", False),
                                                              (32, "fp8_e5m2", False)])

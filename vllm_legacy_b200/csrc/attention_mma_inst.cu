@@ -68,9 +68,10 @@ template <typename T, int KV, int D>
 static int launch_bg(const AttnKernelParams& kp, int num_seqs, cudaStream_t stream) {
   const int G = kp.num_heads / kp.num_kv_heads;
   if (kp.bs_vert_stride > 1) {
-    // block-sparse masks: instantiated for the head sizes the block-sparse models use (phi-3-small: 128); the general
-    // (SIMT) family takes the rest
-    if constexpr (D == 64 || D == 128) {
+    // block-sparse masks: instantiated for the head sizes the block-sparse models use (phi-3-small: 128) and the
+    // reference's test grid (tests/kernels/test_blocksparse_attention.py:29: 64, 112); the general (SIMT) family takes
+    // the rest
+    if constexpr (D == 64 || D == 112 || D == 128) {
       if (kp.block_size == 16)
         return G <= 8 ? launch_one<T, KV, D, 16, 1, true>(kp, num_seqs, stream)
                       : launch_one<T, KV, D, 16, 2, true>(kp, num_seqs, stream);
