@@ -322,17 +322,34 @@ def run_ours(args, rank, world, local_rank):
         o = impl.forward(d_in["query"], d_in["key"], d_in["value"], c["kv_cache"], meta, 1.0)
         h["out"].copy_(o, non_blocking=True)
 
-    for _ in range(3):
-        e2e_step()
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        e2e_step()
-    e1.record()
-    barrier()
-    e2e_ms = e0.elapsed_time(e1)
+    def timed_e2e(one_step):
+        for _ in range(3):
+            one_step()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            one_step()
+        e1.record()
+        barrier()
+        return e0.elapsed_time(e1)
+
+    e2e_eager_ms = timed_e2e(e2e_step)
     e2e_path = ops.last_attention_path()
+    # The same step — H2D copies from the pinned buffers, backend forward, D2H copy — captured ONCE in a CUDA graph and
+    # replayed per step, which is how the reference runs decode (CUDAGraphRunner, vllm/worker/model_runner.py:1066-1158:
+    # persistent input buffers, one replay per step).  Every step still performs every copy and every kernel; what goes
+    # away is the Python / launch overhead of the eager loop, which on a slow or busy host (not on the GPU) decides
+    # whether the GPU is kept fed: eager measured 0.75 ms/step on one box and 0.99 on another for identical GPU work.
+    e2e_mode, e2e_ms = "eager", e2e_eager_ms
+    try:
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            e2e_step()
+        e2e_ms = timed_e2e(graph.replay)
+        e2e_mode = "cuda_graph"
+    except Exception as exc:  # noqa: BLE001 - keep the eager figure
+        sys.stderr.write(f"bench: CUDA-graph capture of the e2e step failed ({type(exc).__name__}: {exc}); eager loop kept\n")
 
     extra = {}
     if world > 1:
@@ -342,10 +359,10 @@ def run_ours(args, rank, world, local_rank):
         extra["weak"] = weak_extra(ops, dist, dev, rank, world, min(args.steps, 50))
 
     # ---- max over ranks ------------------------------------------------------------------------------
-    t = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([total_ms, e2e_ms, e2e_eager_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms = t.tolist()
+    total_ms, e2e_ms, e2e_eager_ms = t.tolist()
     if rank != 0:
         return None
     gbps = total_bytes * args.steps / (total_ms * 1e-3) / 1e9
@@ -367,6 +384,9 @@ def run_ours(args, rank, world, local_rank):
         "e2e": {"value": round(e2e_gbps, 1), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": round(e2e_ms / args.steps, 5),
                 "api": "B200PagedAttentionImpl.forward (reshape_and_cache + forward_decode) from pinned host buffers",
+                "mode": e2e_mode + (" (the step, with its H2D / D2H copies, captured once and replayed per step, as the "
+                                    "reference's CUDAGraphRunner runs decode)" if e2e_mode == "cuda_graph" else ""),
+                "eager_ms_per_step": round(e2e_eager_ms / args.steps, 5),
                 "kernel": e2e_path},
         "gpu_launches": args.steps * launches_per_step,
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": UNIT,
@@ -571,7 +591,16 @@ def prefill_extra(ops, dev, iters=10):
     ms = time_device(lambda: ops.context_attention_fwd(*a), iters)
     tflops = flops / ms / 1e9
     peak = measured_peaks().get("bf16_tflops")
+    # the same step over an fp8 e4m3 KV cache (K [nb, H, D/16, B, 16], V [nb, H, D, B], uint8; random finite codes of
+    # small magnitude): the loader warps dequantise while staging (the reference's kernel has no working fp8 path)
+    def fp8_bytes(*shape):
+        mag = torch.randint(0, 0x38, shape, dtype=torch.uint8, device=dev, generator=g)
+        return mag | (torch.randint(0, 2, shape, dtype=torch.uint8, device=dev, generator=g) << 7)
+    a8 = a[:4] + (fp8_bytes(nseq * nblk, Hkv, D // 16, B, 16), fp8_bytes(nseq * nblk, Hkv, D, B)) + a[6:] + ("fp8", 0.5)
+    ms8 = time_device(lambda: ops.context_attention_fwd(*a8), iters)
     return {"op": "context_attention_fwd (tcgen05 + TMEM prefix-prefill kernel)",
+            "fp8_kv_prefix": {"workload": "same step over an fp8 e4m3 KV cache (kv_scale 0.5), dequantised while staged",
+                              "ms": round(ms8, 4), "algorithmic_tflops": round(flops / ms8 / 1e9, 1)},
             "workload": "8 seqs x 2048 new tokens over 4096 cached, 32q/8kv, head 128, block 16, bf16",
             "ms": round(ms, 4), "algorithmic_tflops": round(tflops, 1), "launches": iters,
             "roofline": {"bound": "tensor", "achieved": round(tflops, 1), "peak": peak, "unit": "TFLOP/s",
