@@ -524,14 +524,16 @@ def configs_extra(ops, dev, peak):
             T * 8 * 128 * 2 * (2 + 1), ms)
     del c4
     torch.cuda.empty_cache()
-    # the general (SIMT) kernel family: what the TMA + mma.sync family does not instantiate (fp32 queries, block size 8)
-    # — coverage kernels, measured so that their distance from the roofline is on record — and block-sparse masks,
-    # which 16-bit queries with head size 64 / 112 / 128 run on the mma family (filtered block iterator)
+    # the general (SIMT) kernel family: what the TMA + mma.sync family does not instantiate (fp32 queries; fp8 caches
+    # with block size 8) — a coverage kernel, measured so that its distance from the roofline is on record — and the two
+    # shapes that moved to the mma family in round 2: block size 8 over a 16-bit cache, and block-sparse masks (head size
+    # 64 / 112 / 128, filtered block iterator)
     S_, L_ = 128, 4096
     attn("simt fp32", "fp32 queries + fp32 cache (x = 4), 32q/8kv, head 128, block 16, 128 x 4096 ctx", [L_] * S_, 32, 8,
          128, 16, dtype=torch.float32, iters=10)
     torch.cuda.empty_cache()
-    attn("simt block8", "block size 8, bf16, 32q/8kv, head 128, 128 x 4096 ctx", [L_] * S_, 32, 8, 128, 8, iters=10)
+    attn("block8", "block size 8, bf16, 32q/8kv, head 128, 128 x 4096 ctx (mma family: one n-tile per block, P.V with "
+         "m16n8k8)", [L_] * S_, 32, 8, 128, 8, iters=10)
     torch.cuda.empty_cache()
     # block-sparse (attention_kernels.cu:212-256): with head_sliding_step 0 a 64-token block k is read when
     # k > q_block - local_blocks or (k + 1) % vert_stride == 0; only those blocks are algorithmic bytes

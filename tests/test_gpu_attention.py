@@ -424,15 +424,51 @@ def test_error_classes(ops):
         ops.paged_attention_v1(torch.empty_like(q), q, kc, vc, 2, 1.0, bt, sl, 16, 64, None, "int8", 1.0)
 
 
+@pytest.mark.parametrize("version", ["v1", "v2"])
+@pytest.mark.parametrize("heads", [(32, 8), (16, 1), (5, 5)])
+@pytest.mark.parametrize("head_size", [64, 112, 128])
+@pytest.mark.parametrize("dtype", [torch.half, torch.bfloat16])
+@pytest.mark.parametrize("alibi", [False, True])
+@torch.inference_mode()
+def test_block8_long_contexts(ops, oracle, version, heads, head_size, dtype, alibi):
+    """Block size 8 on the TMA + mma.sync family (one n-tile per block, P.V with m16n8k8): contexts long enough to
+    wrap every warp's ring many times and to split, lengths ending inside a block, odd numbers of k-steps (head 112)."""
+    torch.manual_seed(11)
+    Hq, Hkv = heads
+    B, NB = 8, 2400
+    lens = [9001, 4100, 1, 8, 9, 1027]
+    S, max_len = len(lens), max(lens)
+    scale = float(head_size ** -0.5)
+    q = torch.empty(S, Hq, head_size, dtype=dtype).uniform_(-scale, scale)
+    kcs, vcs = helpers.create_kv_caches_with_random(NB, B, 1, Hkv, head_size, "auto", dtype, 5, "cpu")
+    kc, vc = kcs[0], vcs[0]
+    nblk = (max_len + B - 1) // B
+    bt = torch.tensor(helpers.make_block_tables(S, nblk, NB, 5), dtype=torch.int32)
+    sl = torch.tensor(lens, dtype=torch.int32)
+    al = torch.randn(Hq, dtype=torch.float32) * 0.1 if alibi else None
+    want = torch.empty_like(q)
+    oracle.paged_attention_v1(want, q, kc, vc, Hkv, scale, bt, sl, B, max_len, al, "auto", 1.0)
+    out = torch.full_like(q, float("nan"), device=DEV)
+    _run(ops, version, out, q.to(DEV), kc.to(DEV), vc.to(DEV), Hkv, scale, bt.to(DEV), sl.to(DEV), B, max_len,
+         al.to(DEV) if al is not None else None, "auto", 1.0)
+    assert ops.last_attention_path() == "mma_tma" and ops.last_attention_partitions() > 1
+    assert not torch.isnan(out).any()
+    ref_mag = want.float().abs().max().item() + 1e-6
+    assert torch.allclose(out.cpu().float(), want.float(), atol=max(1e-3, 1e-3 * ref_mag), rtol=1e-2), \
+        (out.cpu().float() - want.float()).abs().max()
+
+
 def test_mma_family_is_the_one_that_runs(ops):
-    """The 16-bit / block 16|32 configurations must dispatch to the TMA + tensor-core family, not silently to
-    the SIMT one."""
+    """The 16-bit configurations (block 16 | 32, and block 8 over a 16-bit cache) must dispatch to the TMA +
+    tensor-core family, not silently to the SIMT one; fp32 queries and fp8 caches with block 8 stay on the SIMT one."""
     torch.manual_seed(0)
     for (dtype, kvd, B, want) in [(torch.bfloat16, "auto", 16, "mma_tma"), (torch.half, "fp8", 32, "mma_tma"),
-                                  (torch.float, "auto", 16, "simt"), (torch.bfloat16, "auto", 8, "simt")]:
+                                  (torch.float, "auto", 16, "simt"), (torch.bfloat16, "auto", 8, "mma_tma"),
+                                  (torch.half, "fp8", 8, "simt")]:
         q = torch.zeros(2, 32, 128, dtype=dtype, device=DEV)
         kcs, vcs = helpers.create_kv_caches_with_random(8, B, 1, 8, 128, kvd, dtype, 0, DEV, ops.convert_fp8)
-        bt = torch.zeros(2, 4, dtype=torch.int32, device=DEV)
+        bt = torch.zeros(2, (50 + B - 1) // B, dtype=torch.int32, device=DEV)  # enough entries for 50 tokens
         sl = torch.tensor([5, 50], dtype=torch.int32, device=DEV)
         ops.paged_attention_v1(torch.empty_like(q), q, kcs[0], vcs[0], 8, 0.1, bt, sl, B, 50, None, kvd, 1.0)
+        torch.cuda.synchronize()
         assert ops.last_attention_path() == want

@@ -171,12 +171,12 @@ def main():
         timing_case(ref, 256, 32, 8, 128, 16, bf, "auto", 4096, "C2 256x4096 gqa4")
         timing_case(ref, 256, 8, 1, 128, 16, bf, "auto", 8192, "C3/tp8 256x8192 g8")
         timing_case(ref, 128, 32, 8, 128, 16, bf, "fp8", 32768, "C4 128x32k fp8")
-        # the general (SIMT) family: fp32, block size 8, block-sparse (bench.py extra.configs "simt ...")
+        # fp32 queries (the general SIMT family) and the two shapes that moved to the mma family in round 2: block 8, block-sparse
         timing_case(ref, 128, 32, 8, 128, 16, f32, "auto", 4096, "SIMT fp32 128x4096")
-        timing_case(ref, 128, 32, 8, 128, 8, bf, "auto", 4096, "SIMT block8 128x4096")
+        timing_case(ref, 128, 32, 8, 128, 8, bf, "auto", 4096, "block8 128x4096")
         nb, qb = 4096 // 64, (4096 - 1) // 64
         vis = sum(1 for k in range(nb) if k > qb - 16 or (k + 1) % 8 == 0)
-        timing_case(ref, 128, 32, 8, 128, 16, bf, "auto", 4096, "SIMT blocksparse 128x4096", bs=(16, 8, 64, 0),
+        timing_case(ref, 128, 32, 8, 128, 16, bf, "auto", 4096, "blocksparse 128x4096", bs=(16, 8, 64, 0),
                     visible_frac=vis / nb)
 
 

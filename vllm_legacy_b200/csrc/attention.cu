@@ -162,11 +162,13 @@ static int run_attention(const b200pa_attn_params_t* a, bool is_v2, cudaStream_t
   const bool blocksparse = a->blocksparse_vert_stride > 1;
   if (blocksparse && (a->blocksparse_block_size <= 0 || a->blocksparse_block_size % a->block_size != 0))
     return B200PA_ERR_INVALID_ARG;
-  // TMA + mma.sync family: 16-bit queries, block size 16 / 32, 4-byte aligned query rows; dense, or block-sparse for
-  // the head sizes that variant is instantiated for (64, 112, 128)
-  const bool bs_mma = blocksparse && (a->head_size == 64 || a->head_size == 112 || a->head_size == 128);
+  // TMA + mma.sync family: 16-bit queries, block size 16 / 32 (8 for a 16-bit cache), 4-byte aligned query rows; dense,
+  // or block-sparse for the head sizes that variant is instantiated for (64, 112, 128; block 16 / 32)
+  const bool bs_mma = blocksparse && a->block_size != 8 &&
+                      (a->head_size == 64 || a->head_size == 112 || a->head_size == 128);
+  const bool b8_mma = a->block_size != 8 || (a->kv_dtype == B200PA_KV_AUTO && !blocksparse);
   const bool mma_ok = layout == 1 ||
-                      ((!blocksparse || bs_mma) && a->dtype != B200PA_F32 && a->block_size != 8 && tn.force_simt == 0 &&
+                      ((!blocksparse || bs_mma) && a->dtype != B200PA_F32 && b8_mma && tn.force_simt == 0 &&
                        reinterpret_cast<uintptr_t>(a->query) % 4 == 0 && a->q_stride % 2 == 0);
 
   // ---- split plan -----------------------------------------------------------------------

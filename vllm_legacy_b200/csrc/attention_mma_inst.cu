@@ -81,6 +81,11 @@ static int launch_bg(const AttnKernelParams& kp, int num_seqs, cudaStream_t stre
     }
     return 1;
   }
+  if (kp.block_size == 8) {  // 16-bit caches only (an fp8 row of 8 tokens is 8 bytes: the SIMT family keeps those)
+    if constexpr (KV == B200PA_KV_AUTO)
+      return G <= 8 ? launch_one<T, KV, D, 8, 1>(kp, num_seqs, stream) : launch_one<T, KV, D, 8, 2>(kp, num_seqs, stream);
+    return 1;
+  }
   if (kp.block_size == 16)
     return G <= 8 ? launch_one<T, KV, D, 16, 1>(kp, num_seqs, stream) : launch_one<T, KV, D, 16, 2>(kp, num_seqs, stream);
   if (kp.block_size == 32)

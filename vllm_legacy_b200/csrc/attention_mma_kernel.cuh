@@ -137,6 +137,22 @@ __device__ __forceinline__ void mma_16816<__nv_bfloat16>(float (&c)[4], uint32_t
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
+// m16n8k8 (block size 8: one P.V k-step is the block's 8 tokens)
+template <typename MT>
+__device__ __forceinline__ void mma_1688(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0);
+template <>
+__device__ __forceinline__ void mma_1688<__half>(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5}, {%6}, {%0, %1, %2, %3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a0), "r"(a1), "r"(b0));
+}
+template <>
+__device__ __forceinline__ void mma_1688<__nv_bfloat16>(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5}, {%6}, {%0, %1, %2, %3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a0), "r"(a1), "r"(b0));
+}
+
 template <typename MT>
 __device__ __forceinline__ uint32_t pack2(float lo, float hi);
 template <>
@@ -308,7 +324,8 @@ __device__ __forceinline__ void decode_epilogue(const AttnKernelParams& p, uint8
   }
 }
 
-// T: query/out type (half | bf16).  KV: b200pa_kv_dtype_t.  D: head size.  B: block size (16|32).
+// T: query/out type (half | bf16).  KV: b200pa_kv_dtype_t.  D: head size.  B: block size (16 | 32; 8 for 16-bit caches:
+// one 8-token n-tile per block, one ldmatrix.x4 = two k-steps of QK^T, P.V with m16n8k8 whose B operand is the S fragment).
 // NG: 8-row query-head tiles per CTA (1: group <= 8, 2: group <= 16 per CTA).
 // BS: block-sparse masks (attention_kernels.cu:212-256, 387-393).  A warp then walks only the KV blocks that at least
 // one head of the CTA's group attends: consumer and TMA producer step through the same filtered sequence (`nxt`), the
@@ -330,7 +347,7 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
   constexpr int STAGE = 2 * CHUNK;
   constexpr int HPT = 8 * NG;              // query heads per CTA
   constexpr int OROW = D + 4;              // padded row of the merge scratch (floats)
-  static_assert(B == 16 || B == 32, "block size");
+  static_assert(B == 16 || B == 32 || (B == 8 && !FP8), "block size");
   static_assert(D % 16 == 0, "head size");
 
   extern __shared__ __align__(128) uint8_t smem[];
@@ -486,7 +503,10 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
   auto tokmap = [&](int nt, int j) { return TPT * (j >> 1) + 2 * ((nt + rot(j >> 1)) % NP) + (j & 1); };
   const int mi = lane >> 3, mj = lane & 7;
   uint32_t koff[NT / 2 > 0 ? (FP8 ? 2 : NT / 2) : 1];
-  if constexpr (!FP8) {
+  if constexpr (B == 8) {
+    // one call per PAIR of k-steps: matrix mi = d-group 4kp + mi of the block's single n-tile
+    koff[0] = mi * UNIT + tokmap(0, mj) * 16;
+  } else if constexpr (!FP8) {
     // call c of k-step ks: matrices (d-group 2ks + (mi&1), n-tile 2c + (mi>>1))
 #pragma unroll
     for (int c = 0; c < NT / 2; ++c) koff[c] = (mi & 1) * UNIT + tokmap(2 * c + (mi >> 1), mj) * 16;
@@ -540,7 +560,22 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
 #pragma unroll
       for (int e = 0; e < 4; ++e) sacc[nt][e] = 0.f;
 
-    if constexpr (!FP8) {
+    if constexpr (B == 8) {
+#pragma unroll
+      for (int kp = 0; kp < (KS + 1) / 2; ++kp) {
+        // (for an odd KS the last call also reads two d-groups behind the K chunk — the V chunk, same stage — unused)
+        uint32_t r0, r1, r2, r3;
+        ldmatrix_x4(kb + 4 * kp * UNIT + koff[0], r0, r1, r2, r3);
+        if constexpr (NG == 2) {
+          mma_16816<MT>(sacc[0], qa[2 * kp][0], qa[2 * kp][1], qa[2 * kp][2], qa[2 * kp][3], r0, r1);
+          if (2 * kp + 1 < KS)
+            mma_16816<MT>(sacc[0], qa[2 * kp + 1][0], qa[2 * kp + 1][1], qa[2 * kp + 1][2], qa[2 * kp + 1][3], r2, r3);
+        } else {
+          mma_16816<MT>(sacc[0], qa[2 * kp][0], 0u, qa[2 * kp][1], 0u, r0, r1);
+          if (2 * kp + 1 < KS) mma_16816<MT>(sacc[0], qa[2 * kp + 1][0], 0u, qa[2 * kp + 1][1], 0u, r2, r3);
+        }
+      }
+    } else if constexpr (!FP8) {
 #pragma unroll
       for (int ks = 0; ks < KS; ++ks) {
 #pragma unroll
@@ -639,7 +674,9 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
     uint32_t pp[NG][NP];
 #pragma unroll
     for (int r = 0; r < NG; ++r) {
-      if constexpr (NP == 2) {
+      if constexpr (NP == 1) {
+        pp[r][0] = pk[r][0];
+      } else if constexpr (NP == 2) {
         const bool sw = (tig >> 1) != 0;
         pp[r][0] = sw ? pk[r][1] : pk[r][0];
         pp[r][1] = sw ? pk[r][0] : pk[r][1];
@@ -690,7 +727,9 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         const uint32_t addr = vb + (16 * dt + 8 * h) * (B * CTB) + voff;
-        if constexpr (!FP8 && B == 16) {
+        if constexpr (B == 8) {
+          va[h][0] = lds32(addr);  // tokens 2 tig, 2 tig + 1 of row gid (+ 8 h): 128 contiguous bytes per warp
+        } else if constexpr (!FP8 && B == 16) {
           const uint2 v = lds64(addr);
           va[h][0] = v.x; va[h][1] = v.y;
         } else if constexpr (!FP8 && B == 32) {
@@ -708,6 +747,10 @@ __global__ void __launch_bounds__(kMmaThreads, (D * NG <= 256) ? 2 : 1)
 #pragma unroll
           for (int q = 0; q < NP; ++q) va[h][q] &= vmask[q];
         }
+      }
+      if constexpr (B == 8) {
+#pragma unroll
+        for (int r = 0; r < NG; ++r) mma_1688<MT>(oacc[r][dt], va[0][0], va[1][0], pp[r][0]);
       }
 #pragma unroll
       for (int kk = 0; kk < KK; ++kk)
