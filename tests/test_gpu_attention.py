@@ -191,9 +191,9 @@ def test_blocksparse_paged_attention(ops, oracle, version, head_sliding_step, nu
 
 
 @pytest.mark.parametrize("version", ["v1", "v2"])
-@pytest.mark.parametrize("heads", [(8, 2), (32, 4), (32, 2), (24, 1), (6, 6)])   # groups 4, 8, 16, 24 (2 q-tiles), 1
+@pytest.mark.parametrize("heads", [(8, 2), (32, 2), (24, 1)])   # groups 4, 16, 24 (2 q-tiles); 1 and 8: the test above
 @pytest.mark.parametrize("head_size", [64, 112, 128])
-@pytest.mark.parametrize("sparse", [(2, 4, 32, 1), (16, 8, 64, 0), (1, 16, 64, 3), (4, 2, 128, -2), (3, 5, 64, 2)])
+@pytest.mark.parametrize("sparse", [(2, 4, 32, 1), (1, 16, 64, 3), (4, 2, 128, -2)])
 @pytest.mark.parametrize("block_size,kv_cache_dtype,alibi", [(16, "auto", False), (32, "auto", True), (16, "fp8", False),
                                                              (32, "fp8_e5m2", False)])
 @torch.inference_mode()
@@ -204,8 +204,8 @@ def test_blocksparse_mma_family(ops, oracle, version, heads, head_size, sparse, 
     lengths ending inside a block / a sparse block, ALiBi, fp8."""
     torch.manual_seed(7)
     Hq, Hkv = heads
-    D, NB = head_size, 640
-    lens = [1, 63, 64, 700, 4100, 9001]
+    D, NB = head_size, 400
+    lens = [1, 63, 700, 5000]   # (sized for the CPU oracle: the whole GPU suite has to fit the driver's 20-minute step)
     S, max_len = len(lens), max(lens)
     scale = float(D ** -0.5)
     dtype = torch.bfloat16 if kv_cache_dtype != "fp8" else torch.half
@@ -425,9 +425,9 @@ def test_error_classes(ops):
 
 
 @pytest.mark.parametrize("version", ["v1", "v2"])
-@pytest.mark.parametrize("heads", [(32, 8), (16, 1), (5, 5)])
+@pytest.mark.parametrize("heads", [(16, 1), (5, 5)])
 @pytest.mark.parametrize("head_size", [64, 112, 128])
-@pytest.mark.parametrize("dtype", [torch.half, torch.bfloat16])
+@pytest.mark.parametrize("dtype", [torch.bfloat16])   # (fp16 / fp32 / fp8 with block 8: test_paged_attention_vs_oracle)
 @pytest.mark.parametrize("alibi", [False, True])
 @torch.inference_mode()
 def test_block8_long_contexts(ops, oracle, version, heads, head_size, dtype, alibi):
@@ -435,8 +435,8 @@ def test_block8_long_contexts(ops, oracle, version, heads, head_size, dtype, ali
     wrap every warp's ring many times and to split, lengths ending inside a block, odd numbers of k-steps (head 112)."""
     torch.manual_seed(11)
     Hq, Hkv = heads
-    B, NB = 8, 2400
-    lens = [9001, 4100, 1, 8, 9, 1027]
+    B, NB = 8, 1400
+    lens = [9001, 1, 8, 9, 1027]
     S, max_len = len(lens), max(lens)
     scale = float(head_size ** -0.5)
     q = torch.empty(S, Hq, head_size, dtype=dtype).uniform_(-scale, scale)
