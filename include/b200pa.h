@@ -393,8 +393,10 @@ int b200pa_read_stream_probe(const void* src, int64_t bytes, void* sink_u32, b20
 int b200pa_abi_version(void);
 const char* b200pa_status_string(int status);
 int b200pa_last_cuda_error(void); /* cudaError_t of the last B200PA_ERR_CUDA on this thread */
-/* Name of the kernel family the last attention call on this thread dispatched
- * to ("mma_tma" | "simt"), and the number of context splits it used; for tests and the bench. */
+/* Name of the kernel family the last attention call on this thread dispatched to — "mma_tma" (paged layout: dense,
+ * block-sparse and block-8 instantiations of the TMA + mma.sync kernel), "mma_flash" (flash layout), "mma_tma_static"
+ * (static-scratch entry point) or "simt" (general family) — and the number of context splits it used; for tests and
+ * the bench. */
 const char* b200pa_last_attention_path(void);
 int b200pa_last_attention_partitions(void);
 
